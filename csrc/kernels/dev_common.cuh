@@ -1,0 +1,409 @@
+// Device-side building blocks shared by the persistent trainer (K-P) and the
+// stand-alone phase kernels (K-A..K-E).  sm_100a only.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "hpnn_core.h"
+
+namespace hpnn {
+
+constexpr int kThreads = 512;            // CTA size of every engine kernel
+constexpr int kWarps = kThreads / 32;
+constexpr int kRedDoubles = 2 * kThreads;  // shared reduction scratch (8 KB)
+
+// ---- activation: src/ann.c:883-888, cuda_ann.cu:41-61 ----------------------
+__device__ __forceinline__ double act_f(double x) { return 2.0 / (1.0 + exp(-1.0 * x)) - 1.0; }
+__device__ __forceinline__ double dact_f(double y) { return -0.5 * (y * y - 1.0); }
+
+// ---- memory-model helpers --------------------------------------------------
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned *p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned atom_add_acqrel_gpu(unsigned *p, unsigned v) {
+  unsigned old;
+  asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// L2-coherent (L1-bypassing) accesses for everything another CTA / GPU rewrites
+// while a persistent kernel is running.
+__device__ __forceinline__ double ldg_cg(const double *p) { return __ldcg(p); }
+__device__ __forceinline__ double2 ldg_cg2(const double2 *p) { return __ldcg(p); }
+__device__ __forceinline__ void stg_cg(double *p, double v) { __stcg(p, v); }
+__device__ __forceinline__ void stg_cg2(double2 *p, double2 v) { __stcg(p, v); }
+
+// ---- block-wide reductions with a fixed summation order ---------------------
+// Every thread of the CTA gets the same value; `red` needs kWarps doubles.
+__device__ __forceinline__ double block_sum(double v, double *red) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5;
+  __syncthreads();  // protect `red` from the previous use
+  if ((threadIdx.x & 31) == 0) red[w] = v;
+  __syncthreads();
+  double s = 0.0;
+#pragma unroll
+  for (int i = 0; i < kWarps; ++i) s += red[i];
+  return s;
+}
+__device__ __forceinline__ double block_max(double v, double *red) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  const int w = threadIdx.x >> 5;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[w] = v;
+  __syncthreads();
+  double s = red[0];
+#pragma unroll
+  for (int i = 1; i < kWarps; ++i) s = fmax(s, red[i]);
+  return s;
+}
+// first index holding the largest value (ties -> lowest index); NaN never wins
+__device__ __forceinline__ int block_argmax(double v, int idx, double *red) {
+  if (!(v == v)) v = -INFINITY;
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    double ov = __shfl_xor_sync(0xffffffffu, v, o);
+    int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (ov > v || (ov == v && oi < idx)) {
+      v = ov;
+      idx = oi;
+    }
+  }
+  const int w = threadIdx.x >> 5;
+  int *redi = reinterpret_cast<int *>(red + kWarps);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) {
+    red[w] = v;
+    redi[w] = idx;
+  }
+  __syncthreads();
+  double bv = red[0];
+  int bi = redi[0];
+#pragma unroll
+  for (int i = 1; i < kWarps; ++i) {
+    double ov = red[i];
+    int oi = redi[i];
+    if (ov > bv || (ov == bv && oi < bi)) {
+      bv = ov;
+      bi = oi;
+    }
+  }
+  // reference scan starts from probe=-1.0 with a strict '<' (src/ann.c:2346-2351)
+  return (bv > -1.0) ? bi : 0;
+}
+__device__ __forceinline__ int block_max_int(int v, double *red) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  int *redi = reinterpret_cast<int *>(red);
+  const int w = threadIdx.x >> 5;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) redi[w] = v;
+  __syncthreads();
+  int s = redi[0];
+#pragma unroll
+  for (int i = 1; i < kWarps; ++i) s = max(s, redi[i]);
+  return s;
+}
+
+// copy n doubles (n % 2 == 0, 16-byte aligned) global -> shared, bypassing L1
+__device__ __forceinline__ void stage_vec(double *dst, const double *src, int n) {
+  const double2 *s2 = reinterpret_cast<const double2 *>(src);
+  double2 *d2 = reinterpret_cast<double2 *>(dst);
+  for (int i = threadIdx.x; i < (n >> 1); i += blockDim.x) d2[i] = ldg_cg2(s2 + i);
+}
+
+// where a forward result goes: the same offset in up to HPNN_MAX_WORLD buffers
+// (all-gather by peer stores when n > 1)
+struct Dst {
+  double *p[HPNN_MAX_WORLD];
+  int n;
+};
+
+// ---------------------------------------------------------------------------
+// Row tasks (K-A / K-D / K-E): one warp per owned row.
+//   UPD 0: y = f(w.x)
+//   UPD 1: w += (lr*delta_r) * x ; y = f(w.x)                       (BP)
+//   UPD 2: m += (lr*delta_r) * x ; w += m ; m *= alpha ; y = f(w.x)  (BPM)
+// xs: input vector in shared memory (ld doubles, pad = 0); ds: local deltas.
+// ---------------------------------------------------------------------------
+template <int UPD>
+__device__ __forceinline__ double warp_row(double *wrow, double *mrow, const double *xs, int ld, double s,
+                                           double alpha, int lane) {
+  double2 *w2 = reinterpret_cast<double2 *>(wrow);
+  double2 *m2 = reinterpret_cast<double2 *>(mrow);
+  const double2 *x2 = reinterpret_cast<const double2 *>(xs);
+  const int n2 = ld >> 1;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  int i = lane;
+  for (; i + 96 < n2; i += 128) {
+    double2 w[4], m[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) w[u] = ldg_cg2(w2 + i + 32 * u);
+    if (UPD == 2) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) m[u] = ldg_cg2(m2 + i + 32 * u);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const double2 x = x2[i + 32 * u];
+      if (UPD == 1) {
+        w[u].x = fma(s, x.x, w[u].x);
+        w[u].y = fma(s, x.y, w[u].y);
+        stg_cg2(w2 + i + 32 * u, w[u]);
+      } else if (UPD == 2) {
+        m[u].x = fma(s, x.x, m[u].x);
+        m[u].y = fma(s, x.y, m[u].y);
+        w[u].x += m[u].x;
+        w[u].y += m[u].y;
+        stg_cg2(w2 + i + 32 * u, w[u]);
+        m[u].x *= alpha;
+        m[u].y *= alpha;
+        stg_cg2(m2 + i + 32 * u, m[u]);
+      }
+      double &a = (u == 0) ? a0 : (u == 1) ? a1 : (u == 2) ? a2 : a3;
+      a = fma(w[u].x, x.x, a);
+      a = fma(w[u].y, x.y, a);
+    }
+  }
+  for (; i < n2; i += 32) {
+    double2 w = ldg_cg2(w2 + i);
+    const double2 x = x2[i];
+    if (UPD == 1) {
+      w.x = fma(s, x.x, w.x);
+      w.y = fma(s, x.y, w.y);
+      stg_cg2(w2 + i, w);
+    } else if (UPD == 2) {
+      double2 m = ldg_cg2(m2 + i);
+      m.x = fma(s, x.x, m.x);
+      m.y = fma(s, x.y, m.y);
+      w.x += m.x;
+      w.y += m.y;
+      stg_cg2(w2 + i, w);
+      m.x *= alpha;
+      m.y *= alpha;
+      stg_cg2(m2 + i, m);
+    }
+    a0 = fma(w.x, x.x, a0);
+    a0 = fma(w.y, x.y, a0);
+  }
+  double a = (a0 + a1) + (a2 + a3);
+#pragma unroll
+  for (int o = 16; o; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  return a;
+}
+
+// all owned rows of one layer, spread over the whole grid; result r goes to
+// dst.p[q][r] for every q (caller pre-offsets the pointers to the owned slice)
+template <int UPD>
+__device__ __forceinline__ void phase_rows(double *W, double *dW, int ld, int rows, const double *xs,
+                                           const double *ds, double lr, double alpha, int act_kind,
+                                           const Dst &dst) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int r = blockIdx.x + gridDim.x * warp; r < rows; r += gridDim.x * kWarps) {
+    double *wrow = W + (size_t)r * ld;
+    double *mrow = (UPD == 2) ? dW + (size_t)r * ld : nullptr;
+    const double s = UPD ? lr * ds[r] : 0.0;
+    const double z = warp_row<UPD>(wrow, mrow, xs, ld, s, alpha, lane);
+    if (lane == 0) {
+      const double y = act_kind == 0 ? act_f(z) : z;
+      for (int q = 0; q < dst.n; ++q) stg_cg(dst.p[q] + r, y);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Column tasks (K-C fused with K-D/K-E): one CTA owns CB columns of the local
+// row block, reads every row segment once, accumulates W^T.delta from the OLD
+// weights and applies the BP/BPM update in the same pass.
+// The CB partial sums are handed to `sink(col_in_block, value)` by threads < CB.
+// ---------------------------------------------------------------------------
+template <int CB, int UPD, typename Sink>
+__device__ __forceinline__ void col_task(double *W, double *dW, int ld, int rows, int c0, const double *ds,
+                                         const double *h, double lr, double alpha, double *red, Sink sink) {
+  constexpr int TPR = CB / 2;          // threads per row segment (double2 each)
+  constexpr int RL = kThreads / TPR;   // row lanes
+  const int cp = threadIdx.x % TPR, rl = threadIdx.x / TPR;
+  const int c = c0 + 2 * cp;
+  double h0 = 0.0, h1 = 0.0;
+  if (UPD) {
+    h0 = ldg_cg(h + c);
+    h1 = ldg_cg(h + c + 1);
+  }
+  double a0 = 0.0, a1 = 0.0;
+  const size_t stride2 = (size_t)(ld >> 1);
+  double2 *Wp = reinterpret_cast<double2 *>(W + c);
+  double2 *Mp = reinterpret_cast<double2 *>((UPD == 2 ? dW : W) + c);
+  int r = rl;
+  for (; r + 3 * RL < rows; r += 4 * RL) {
+    double2 w[4], m[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) w[u] = ldg_cg2(Wp + (size_t)(r + u * RL) * stride2);
+    if (UPD == 2) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) m[u] = ldg_cg2(Mp + (size_t)(r + u * RL) * stride2);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const double d = ds[r + u * RL];
+      a0 = fma(w[u].x, d, a0);
+      a1 = fma(w[u].y, d, a1);
+      if (UPD == 1) {
+        const double s = lr * d;
+        w[u].x = fma(s, h0, w[u].x);
+        w[u].y = fma(s, h1, w[u].y);
+        stg_cg2(Wp + (size_t)(r + u * RL) * stride2, w[u]);
+      } else if (UPD == 2) {
+        const double s = lr * d;
+        m[u].x = fma(s, h0, m[u].x);
+        m[u].y = fma(s, h1, m[u].y);
+        w[u].x += m[u].x;
+        w[u].y += m[u].y;
+        stg_cg2(Wp + (size_t)(r + u * RL) * stride2, w[u]);
+        m[u].x *= alpha;
+        m[u].y *= alpha;
+        stg_cg2(Mp + (size_t)(r + u * RL) * stride2, m[u]);
+      }
+    }
+  }
+  for (; r < rows; r += RL) {
+    double2 w = ldg_cg2(Wp + (size_t)r * stride2);
+    const double d = ds[r];
+    a0 = fma(w.x, d, a0);
+    a1 = fma(w.y, d, a1);
+    if (UPD == 1) {
+      const double s = lr * d;
+      w.x = fma(s, h0, w.x);
+      w.y = fma(s, h1, w.y);
+      stg_cg2(Wp + (size_t)r * stride2, w);
+    } else if (UPD == 2) {
+      double2 m = ldg_cg2(Mp + (size_t)r * stride2);
+      const double s = lr * d;
+      m.x = fma(s, h0, m.x);
+      m.y = fma(s, h1, m.y);
+      w.x += m.x;
+      w.y += m.y;
+      stg_cg2(Wp + (size_t)r * stride2, w);
+      m.x *= alpha;
+      m.y *= alpha;
+      stg_cg2(Mp + (size_t)r * stride2, m);
+    }
+  }
+  // row lanes inside a warp share a column pair when lane % TPR matches
+#pragma unroll
+  for (int o = 16; o >= TPR; o >>= 1) {
+    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();  // `red` may still be read by the previous task
+  if (lane < TPR && lane < 32) {
+    red[warp * CB + 2 * lane] = a0;
+    red[warp * CB + 2 * lane + 1] = a1;
+  }
+  __syncthreads();
+  if (threadIdx.x < CB) {
+    double s = 0.0;
+    // with TPR == 32 (CB == 64) every warp holds one row lane; otherwise kWarps partials
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) s += red[w * CB + threadIdx.x];
+    sink(threadIdx.x, s);
+  }
+}
+
+template <int UPD, typename SinkFactory>
+__device__ __forceinline__ void phase_cols(double *W, double *dW, int ld, int rows, int cb, const double *ds,
+                                           const double *h, double lr, double alpha, double *red,
+                                           SinkFactory make_sink) {
+  const int ntasks = ld / cb;
+  for (int t = blockIdx.x; t < ntasks; t += gridDim.x) {
+    const int c0 = t * cb;
+    auto sink = make_sink(c0);
+    if (cb == 8) col_task<8, UPD>(W, dW, ld, rows, c0, ds, h, lr, alpha, red, sink);
+    else if (cb == 16) col_task<16, UPD>(W, dW, ld, rows, c0, ds, h, lr, alpha, red, sink);
+    else col_task<32, UPD>(W, dW, ld, rows, c0, ds, h, lr, alpha, red, sink);
+  }
+}
+
+__host__ __device__ inline int pick_col_block(int ld, int grid) {
+  if (ld % 32 == 0 && ld / 32 >= 2 * grid) return 32;
+  if (ld % 16 == 0 && ld / 16 >= 2 * grid) return 16;
+  return 8;
+}
+
+// ---------------------------------------------------------------------------
+// Output statistics (K-B), computed redundantly by every CTA from the gathered
+// output vector: softmax (SNN), error, argmax, target index, output deltas.
+// ---------------------------------------------------------------------------
+struct OutStats {
+  double err;
+  int argmax;
+  int target;
+};
+
+// z: gathered output (ANN: activated, SNN: raw).  For SNN the normalised output
+// is exp(z-1)/(TINY+sum) (src/snn.c:282-334) unless stable.  ds receives the
+// deltas of rows [row0,row0+rows) when non-null; o_out (global) the outputs.
+__device__ __forceinline__ OutStats output_stats(int type, int stable, const double *z, const double *t,
+                                                 int n, int row0, int rows, double *ds, double *o_out,
+                                                 double *red) {
+  OutStats st;
+  double shift = 1.0, dv = 1.0;
+  if (type == HPNN_TYPE_SNN) {
+    if (stable) {
+      double m = -INFINITY;
+      for (int j = threadIdx.x; j < n; j += blockDim.x) m = fmax(m, ldg_cg(z + j));
+      shift = block_max(m, red);
+    }
+    double s = 0.0;
+    for (int j = threadIdx.x; j < n; j += blockDim.x) s += exp(ldg_cg(z + j) - shift);
+    dv = block_sum(s, red) + HPNN_TINY;
+  }
+  double e = 0.0, best = -INFINITY;
+  int besti = 0x7fffffff, trg = -1;
+  for (int j = threadIdx.x; j < n; j += blockDim.x) {
+    double o = ldg_cg(z + j);
+    if (type == HPNN_TYPE_SNN) o = exp(o - shift) / dv;
+    const double tj = ldg_cg(t + j);
+    double d;
+    if (type == HPNN_TYPE_SNN) {
+      if (o > 0.) e += tj * log(o + HPNN_TINY);
+      d = tj - o;
+    } else {
+      e += (tj - o) * (tj - o);
+      d = (tj - o) * dact_f(o);
+    }
+    if (ds && j >= row0 && j < row0 + rows) ds[j - row0] = d;
+    if (o_out) stg_cg(o_out + j, o);
+    if (o > best) {  // ascending j per thread: keeps the first maximum
+      best = o;
+      besti = j;
+    }
+    if (tj == 1.0) trg = j;
+  }
+  e = block_sum(e, red);
+  st.err = (type == HPNN_TYPE_SNN) ? e * (-1.0 / n) : 0.5 * e;
+  st.argmax = block_argmax(best, besti, red);
+  trg = block_max_int(trg, red);
+  st.target = trg < 0 ? 0 : trg;
+  __syncthreads();
+  return st;
+}
+
+}  // namespace hpnn

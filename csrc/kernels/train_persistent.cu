@@ -1,0 +1,338 @@
+// K-P: the persistent per-sample trainer.  One cooperative launch per sample runs
+// the whole convergence loop of ann_train_BP/BPM / snn_train_BP/BPM
+// (src/ann.c:2281-2467, src/snn.c:1417-1595) on the device: the host is involved
+// once per sample instead of ~40 times per iteration.
+//
+// Per iteration (weight layers 0..NL-1):
+//   top-down   l = NL-1..1 : column tasks -> partial W_l^T.delta_l from the OLD
+//                            weights, BP/BPM update of W_l in the same pass, partials
+//                            pushed to the rank owning the matching rows of layer l-1
+//                            (reduce-scatter by peer stores)               [barrier]
+//   bottom-up  l = 0       : row tasks: update W_0 and forward in one pass  [barrier]
+//              l = 1..NL-1 : row tasks: forward with the new weights; every result is
+//                            stored into all ranks' activation buffers
+//                            (all-gather by peer stores)                    [barrier]
+//   every CTA then evaluates softmax / error / argmax / loop test redundantly.
+// => 2*NL-1 barriers and 3 passes over W (5 with momentum) per iteration, against the
+// reference's ~3*NL+4 device-wide syncs and 5 (9) passes.
+#include <stdio.h>
+
+#include "dev_common.cuh"
+
+namespace hpnn {
+
+struct KP {
+  hpnn_dev_net net;
+  int type, train, mode, stable;
+  double lr, alpha, thr;
+  int min_iter, max_iter;
+  int max_ld, max_rows;  // shared-memory carve-up (doubles)
+  hpnn_train_result *result;
+};
+
+// Grid barrier, extended to all ranks when world > 1.  The sense is a
+// monotonically increasing epoch; the last CTA to arrive on a rank does the
+// cross-rank exchange (one release-store per peer + acquire-spin on its own
+// flag words) before releasing its grid.
+struct Barrier {
+  unsigned *count, *release, *wepoch;
+  unsigned epoch;  // meaningful in thread 0
+  __device__ __forceinline__ void init(const hpnn_dev_net &n) {
+    count = n.local_sync;
+    release = n.local_sync + 1;
+    wepoch = n.local_sync + 2;
+    epoch = (threadIdx.x == 0) ? ld_acquire_gpu(release) : 0u;
+  }
+  __device__ __forceinline__ void sync(const hpnn_dev_net &n) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      ++epoch;
+      if (n.world > 1) fence_sys();  // this CTA's peer stores are ordered before the arrive
+      const unsigned old = atom_add_acqrel_gpu(count, 1u);
+      if (old == gridDim.x - 1) {
+        *count = 0;  // nobody can arrive again before the release below
+        if (n.world > 1) {
+          const unsigned long long we = (unsigned long long)(++(*wepoch));
+          fence_sys();
+          for (int q = 0; q < n.world; ++q) {
+            if (q == n.rank) continue;
+            unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
+            st_release_sys(f, we);
+          }
+          const unsigned long long *mine =
+              reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
+          for (int q = 0; q < n.world; ++q) {
+            if (q == n.rank) continue;
+            while (ld_acquire_sys(mine + q) < we) {
+            }
+          }
+        }
+        st_release_gpu(release, epoch);
+      } else {
+        while (ld_acquire_gpu(release) != epoch) {
+        }
+      }
+      if (n.world > 1) fence_sys();
+    }
+    __syncthreads();
+  }
+};
+
+__device__ __forceinline__ int pad8(int v) { return (v + 7) & ~7; }
+// inverse of row0(g) = floor(g*n/world)
+__device__ __forceinline__ int owner_of_row(int row, int n, int world) {
+  return (int)(((long long)(row + 1) * world - 1) / n);
+}
+__device__ __forceinline__ int row0_of(int g, int n, int world) { return (int)((long long)g * n / world); }
+
+// delta_l[r] = dact(h_l[r]) * sum_g part_l[g][r] for the owned rows, into shared memory
+__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, const double *act_next, double *ds) {
+  const double *part = n.arena[n.rank] + n.off_part[l];
+  const int stride = n.part_stride[l];
+  for (int r = threadIdx.x; r < n.rows[l]; r += blockDim.x) {
+    double s = 0.0;
+    for (int g = 0; g < n.world; ++g) s += ldg_cg(part + (size_t)g * stride + r);
+    ds[r] = s * dact_f(ldg_cg(act_next + n.row0[l] + r));
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_constant__ KP p) {
+  extern __shared__ double smem[];
+  double *xs = smem;
+  double *ds = xs + p.max_ld;
+  double *red = ds + p.max_rows;
+
+  const hpnn_dev_net &n = p.net;
+  const int NL = n.n_layers;
+  const int n_out = n.dims[NL];
+  double *A = n.arena[n.rank];
+  const bool snn = p.type == HPNN_TYPE_SNN;
+  const int upd = (p.train == HPNN_TRAIN_BPM) ? 2 : 1;
+  const int grid = gridDim.x;
+
+  Barrier bar;
+  bar.init(n);
+
+  // act[i], i >= 1, is double buffered: the fused update+forward of layer 0 rewrites
+  // act[1] while other CTAs may still need the old values to finish delta_0.
+  int cur = 0;
+  auto act_of = [&](int rank, int i, int buf) -> double * {
+    return n.arena[rank] + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]));
+  };
+  auto forward_layer = [&](int l, int src_buf, int dst_buf, int u) {
+    stage_vec(xs, act_of(n.rank, l, src_buf), n.ld[l]);
+    __syncthreads();
+    Dst dst;
+    dst.n = n.world;
+    for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + n.row0[l];
+    const int kind = (snn && l == NL - 1) ? 1 : 0;
+    if (u == 0) phase_rows<0>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, 0.0, 0.0, kind, dst);
+    else if (u == 1) phase_rows<1>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst);
+    else phase_rows<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst);
+  };
+
+  // ---- prologue: zero the momentum (per sample, src/ann.c:2386), first forward
+  if (p.mode == 0 && upd == 2) {
+    for (int l = 0; l < NL; ++l) {
+      double2 *m2 = reinterpret_cast<double2 *>(n.dW[l]);
+      const size_t tot = (size_t)n.rows[l] * n.ld[l] / 2;
+      for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (size_t)grid * blockDim.x)
+        stg_cg2(m2 + i, make_double2(0.0, 0.0));
+    }
+  }
+  for (int l = 0; l < NL; ++l) {
+    forward_layer(l, cur, cur, 0);
+    bar.sync(n);
+  }
+  const double *target = A + n.off_target;
+  const int last = NL - 1;
+  OutStats st = output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, n.row0[last],
+                             n.rows[last], ds, (p.mode == 1 && blockIdx.x == 0) ? A + n.off_out : nullptr, red);
+  double E = st.err;
+  const double init_err = E;
+  int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
+  double dE = 0.0;
+
+  if (p.mode == 0) {
+    for (;;) {
+      ++iter;
+      // ---- top-down: deltas from the old weights fused with the update
+      for (int l = last; l >= 1; --l) {
+        if (l != last) {
+          stage_delta(n, l, act_of(n.rank, l + 1, cur), ds);
+          __syncthreads();
+        }
+        const int cols = n.dims[l];
+        const int cb = pick_col_block(n.ld[l], grid);
+        const long long off_prev = n.off_part[l - 1];
+        const int stride_prev = n.part_stride[l - 1];
+        auto make_sink = [&](int c0) {
+          return [=, &n](int i, double v) {
+            const int col = c0 + i;
+            if (col < cols) {
+              const int own = owner_of_row(col, cols, n.world);
+              double *dstp = n.arena[own] + off_prev + (size_t)n.rank * stride_prev +
+                             (col - row0_of(own, cols, n.world));
+              stg_cg(dstp, v);
+            }
+          };
+        };
+        const double *h = act_of(n.rank, l, cur);
+        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, ds, h, p.lr, p.alpha, red, make_sink);
+        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, ds, h, p.lr, p.alpha, red, make_sink);
+        bar.sync(n);
+      }
+      // ---- bottom-up: layer 0 update fused with its forward, then the rest
+      stage_delta(n, 0, act_of(n.rank, 1, cur), ds);
+      forward_layer(0, 0, cur ^ 1, upd);
+      bar.sync(n);
+      for (int l = 1; l < NL; ++l) {
+        forward_layer(l, cur ^ 1, cur ^ 1, 0);
+        bar.sync(n);
+      }
+      cur ^= 1;
+      // ---- evaluate (every CTA, identical arithmetic => identical decision)
+      st = output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, n.row0[last], n.rows[last],
+                        ds, nullptr, red);
+      dE = E - st.err;
+      E = st.err;
+      ok = (st.argmax == st.target);
+      if (iter == 1) first_ok = ok;
+      if (iter > p.max_iter) break;
+      ok = ok && (iter > p.min_iter);
+      if (!(dE > p.thr || !ok)) break;
+    }
+    // publish the final (normalised) output vector
+    if (blockIdx.x == 0)
+      output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, 0, 0, nullptr, A + n.off_out, red);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && p.result) {
+    hpnn_train_result r;
+    r.init_err = init_err;
+    r.final_de = dE;
+    r.last_err = E;
+    r.n_iter = iter;
+    r.first_ok = first_ok;
+    r.success = ok;
+    r.reserved = st.argmax;
+    *p.result = r;
+  }
+}
+
+// ------------------------------- host side ---------------------------------
+static int g_grid_override = 0;
+static thread_local char g_err[512] = "";
+long long g_launches = 0;
+
+void set_error(const char *what, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+}
+void set_error_msg(const char *what) { snprintf(g_err, sizeof(g_err), "%s", what); }
+
+}  // namespace hpnn
+
+using namespace hpnn;
+
+extern "C" {
+
+const char *hpnn_last_error(void) { return g_err; }
+
+long long hpnn_dev_launch_count(int reset) {
+  long long v = g_launches;
+  if (reset) g_launches = 0;
+  return v;
+}
+
+void hpnn_dev_set_persistent_grid(int ctas) { g_grid_override = ctas; }
+
+int hpnn_dev_persistent_grid(void) {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (g_grid_override > 0 && g_grid_override <= sms) return g_grid_override;
+  return sms;
+}
+
+long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
+  if (!net || net->n_layers < 2 || net->n_layers > HPNN_MAX_LAYERS || net->world < 1 ||
+      net->world > HPNN_MAX_WORLD || net->rank < 0 || net->rank >= net->world)
+    return -1;
+  const int NL = net->n_layers, W = net->world;
+  auto pad = [](long long v) { return (v + 7) & ~7LL; };
+  long long off = 0;
+  for (int l = 0; l < NL; ++l) {
+    const int N = net->dims[l + 1];
+    net->ld[l] = (int)pad(net->dims[l]);
+    net->row0[l] = (int)((long long)net->rank * N / W);
+    net->rows[l] = (int)((long long)(net->rank + 1) * N / W) - net->row0[l];
+    net->part_stride[l] = (int)pad((N + W - 1) / W);
+  }
+  for (int i = 0; i <= NL; ++i) {
+    net->off_act[i] = off;
+    off += pad(net->dims[i]) * (i == 0 ? 1 : 2);
+  }
+  for (int l = 0; l < NL; ++l) {
+    net->off_part[l] = off;
+    off += (long long)W * net->part_stride[l];
+  }
+  net->off_target = off;
+  off += pad(net->dims[NL]);
+  net->off_out = off;
+  off += pad(net->dims[NL]);
+  net->off_flags = off;
+  off += 2 * HPNN_MAX_WORLD;
+  net->arena_doubles = off;
+  return off;
+}
+
+int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
+                          hpnn_train_result *result_dev, void *stream) {
+  if (!net || !o) return -1;
+  KP p;
+  p.net = *net;
+  hpnn_train_opts d;
+  hpnn_train_opts_default(&d, o->type, o->train, 1);
+  p.type = o->type;
+  p.train = o->train;
+  p.mode = mode;
+  p.stable = o->stable_softmax;
+  p.lr = o->lr > 0 ? o->lr : d.lr;
+  p.alpha = o->alpha;
+  p.thr = o->delta > 0 ? o->delta : d.delta;
+  p.min_iter = o->min_iter >= 0 ? o->min_iter : d.min_iter;
+  p.max_iter = o->max_iter >= 0 ? o->max_iter : d.max_iter;
+  p.result = result_dev;
+  int max_ld = 8, max_rows = 8;
+  for (int l = 0; l < net->n_layers; ++l) {
+    max_ld = net->ld[l] > max_ld ? net->ld[l] : max_ld;
+    max_rows = net->rows[l] > max_rows ? net->rows[l] : max_rows;
+    if (mode == 0 && o->train == HPNN_TRAIN_BPM && !net->dW[l]) {
+      set_error_msg("hpnn_dev_train_sample: BPM needs momentum buffers");
+      return -1;
+    }
+  }
+  p.max_ld = max_ld;
+  p.max_rows = (max_rows + 7) & ~7;
+  const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles);
+  if (smem > 227 * 1024) {
+    set_error_msg("hpnn_dev_train_sample: layer too wide for the persistent kernel (use the multi-launch path)");
+    return -2;
+  }
+  cudaError_t e = cudaFuncSetAttribute(k_train_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(k_train_sample)", e);
+    return -1;
+  }
+  const int grid = hpnn_dev_persistent_grid();
+  void *args[] = {(void *)&p};
+  e = cudaLaunchCooperativeKernel((const void *)k_train_sample, dim3(grid), dim3(kThreads), args, smem,
+                                  (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("cudaLaunchCooperativeKernel(k_train_sample)", e);
+    return -1;
+  }
+  ++g_launches;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,274 @@
+"""``HpnnNet``: a feed-forward ANN / SNN resident on one B200, or row-split over the
+GPUs of one NVLink domain (one process per GPU).
+
+Design, on purpose different from the reference:
+  * weights are *truly partitioned*: rank ``g`` holds rows ``[g*N/P, (g+1)*N/P)`` of every
+    layer in its own HBM (the reference keeps everything on GPU 0 in P2P mode and a full
+    replica per GPU in EXP mode, src/cuda_ann.cu:197-254);
+  * every rank owns a small symmetric "arena" (activations, partial deltas, barrier
+    flags) that all peers map through CUDA IPC; the persistent kernel all-gathers
+    activations and reduce-scatters deltas by storing straight into the peers' arenas;
+  * the whole per-sample convergence loop is one cooperative kernel launch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import _native as N
+from ..kernel_io import Kernel
+
+
+class _DevBuf:
+    """Expose raw device memory to torch through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, n_doubles: int):
+        self.__cuda_array_interface__ = {"shape": (n_doubles,), "typestr": "<f8", "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+def pad8(v: int) -> int:
+    return (v + 7) & ~7
+
+
+def split_rows(n: int, rank: int, world: int):
+    """Balanced row split: rank owns ``[rank*n//world, (rank+1)*n//world)``."""
+    r0 = rank * n // world
+    return r0, (rank + 1) * n // world - r0
+
+
+class HpnnNet:
+    def __init__(self, kernel: Kernel, nn_type: int, device: Optional[torch.device] = None,
+                 momentum: bool = True, group=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("HpnnNet needs a CUDA device (use the 'cpu' or 'torch' engine otherwise)")
+        self.lib = N.load()
+        self.type = int(nn_type)
+        self.dims = list(kernel.dims)
+        self.name = kernel.name
+        self.group = group
+        if group is not None:
+            import torch.distributed as dist
+            self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        else:
+            self.rank, self.world = 0, 1
+        if self.world > N.MAX_WORLD:
+            raise ValueError(f"at most {N.MAX_WORLD} ranks per NVLink domain")
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        torch.cuda.set_device(self.device)
+        NL = len(self.dims) - 1
+        if NL < 2 or NL > N.MAX_LAYERS:
+            raise ValueError("need 1..%d hidden layers" % (N.MAX_LAYERS - 1))
+        net = N.DevNet()
+        net.n_layers = NL
+        for i, d in enumerate(self.dims):
+            net.dims[i] = d
+        net.rank, net.world = self.rank, self.world
+        n_doubles = self.lib.hpnn_dev_arena_layout(C.byref(net))
+        if n_doubles <= 0:
+            raise ValueError("invalid network layout")
+        self.net = net
+        # ---- weights (+ momentum): private, padded leading dimension, owned rows only
+        self.W_full: List[torch.Tensor] = []
+        self.dW_full: List[Optional[torch.Tensor]] = []
+        for l in range(NL):
+            Wl = torch.zeros((net.rows[l], net.ld[l]), dtype=torch.float64, device=self.device)
+            r0 = net.row0[l]
+            src = torch.from_numpy(np.ascontiguousarray(kernel.weights[l][r0:r0 + net.rows[l]]))
+            Wl[:, : self.dims[l]].copy_(src)
+            self.W_full.append(Wl)
+            net.W[l] = Wl.data_ptr() if Wl.numel() else None
+            if momentum:
+                Ml = torch.zeros_like(Wl)
+                self.dW_full.append(Ml)
+                net.dW[l] = Ml.data_ptr() if Ml.numel() else None
+            else:
+                self.dW_full.append(None)
+                net.dW[l] = None
+        # ---- symmetric arena + private sync words (raw cudaMalloc: IPC-exportable)
+        self._arena_ptr = self.lib.hpnn_dev_alloc(n_doubles * 8)
+        self._sync_ptr = self.lib.hpnn_dev_alloc(64 * 4)
+        if not self._arena_ptr or not self._sync_ptr:
+            raise MemoryError(N.last_error())
+        self.arena = torch.as_tensor(_DevBuf(self._arena_ptr, n_doubles), device=self.device)
+        net.local_sync = self._sync_ptr
+        self._peer_ptrs: List[int] = []
+        for q in range(N.MAX_WORLD):
+            net.arena[q] = None
+        net.arena[self.rank] = self._arena_ptr
+        if self.world > 1:
+            self._exchange_arenas()
+        # ---- per-sample staging: pinned result ring + device result slots
+        self._n_slots = 1024
+        self._res_dev = torch.zeros(self._n_slots * C.sizeof(N.TrainResult) // 8, dtype=torch.float64,
+                                    device=self.device)
+        self._res_host = torch.zeros_like(self._res_dev, device="cpu").pin_memory()
+        self._closed = False
+
+    # ------------------------------------------------------------------ set-up
+    def _exchange_arenas(self):
+        import torch.distributed as dist
+
+        handle = C.create_string_buffer(64)
+        N.check(self.lib.hpnn_ipc_export(self._arena_ptr, handle), "hpnn_ipc_export")
+        mine = (self.rank, self.device.index, bytes(handle.raw))
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=self.group)
+        for rank, _dev, raw in everyone:
+            if rank == self.rank:
+                continue
+            p = self.lib.hpnn_ipc_open(raw)
+            if not p:
+                raise RuntimeError("hpnn_ipc_open: " + N.last_error())
+            self._peer_ptrs.append(p)
+            self.net.arena[rank] = p
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def close(self):
+        if getattr(self, "_closed", True):
+            return
+        self._closed = True
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)
+        for p in self._peer_ptrs:
+            self.lib.hpnn_ipc_close(p)
+        self.arena = None
+        self.lib.hpnn_dev_free(self._arena_ptr)
+        self.lib.hpnn_dev_free(self._sync_ptr)
+
+    def __del__(self):
+        try:
+            if self.world == 1:
+                self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ views
+    @property
+    def n_layers(self) -> int:
+        return len(self.dims) - 1
+
+    @property
+    def weights(self) -> List[torch.Tensor]:
+        """Owned rows of every layer, ``[rows_l, dims[l]]`` views into the padded storage."""
+        return [W[:, : self.dims[l]] for l, W in enumerate(self.W_full)]
+
+    def _slice(self, off: int, n: int) -> torch.Tensor:
+        return self.arena[off: off + n]
+
+    @property
+    def input_buf(self) -> torch.Tensor:
+        return self._slice(self.net.off_act[0], self.dims[0])
+
+    @property
+    def target_buf(self) -> torch.Tensor:
+        return self._slice(self.net.off_target, self.dims[-1])
+
+    @property
+    def output_buf(self) -> torch.Tensor:
+        return self._slice(self.net.off_out, self.dims[-1])
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ------------------------------------------------------------------ per-sample ops
+    def make_opts(self, train: int, lr: Optional[float] = None, alpha: float = 0.2, delta: float = -1.0,
+                  min_iter: int = -1, max_iter: int = -1, stable_softmax: bool = False) -> N.TrainOpts:
+        o = N.TrainOpts()
+        self.lib.hpnn_train_opts_default(C.byref(o), self.type, int(train), 1)
+        if lr is not None and lr > 0:
+            o.lr = lr
+        o.alpha = alpha
+        if delta > 0:
+            o.delta = delta
+        if min_iter >= 0:
+            o.min_iter = min_iter
+        if max_iter >= 0:
+            o.max_iter = max_iter
+        o.stable_softmax = int(stable_softmax)
+        return o
+
+    def load_sample(self, x: torch.Tensor, t: Optional[torch.Tensor] = None) -> None:
+        """Stream-ordered copy of one sample into the arena (H2D when ``x`` is pinned host memory)."""
+        self.input_buf.copy_(x, non_blocking=True)
+        if t is not None:
+            self.target_buf.copy_(t, non_blocking=True)
+
+    def train_sample_async(self, opts: N.TrainOpts, slot: int = 0) -> None:
+        """Enqueue the persistent trainer for the sample currently in the arena."""
+        res_ptr = self._res_dev.data_ptr() + (slot % self._n_slots) * C.sizeof(N.TrainResult)
+        N.check(self.lib.hpnn_dev_train_sample(C.byref(self.net), C.byref(opts), 0, res_ptr, self._stream()),
+                "hpnn_dev_train_sample")
+
+    def fetch_results(self, n: int = 1) -> List[N.TrainResult]:
+        """D2H of the first ``n`` result slots (synchronises the stream)."""
+        n = min(n, self._n_slots)
+        nd = n * C.sizeof(N.TrainResult) // 8
+        self._res_host[:nd].copy_(self._res_dev[:nd], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        buf = self._res_host.numpy()
+        arr = (N.TrainResult * n).from_buffer_copy(buf[:nd].tobytes())
+        return list(arr)
+
+    def train_sample(self, x: torch.Tensor, t: torch.Tensor, opts: N.TrainOpts) -> N.TrainResult:
+        self.load_sample(x, t)
+        self.train_sample_async(opts, 0)
+        return self.fetch_results(1)[0]
+
+    def run(self, x: torch.Tensor, t: Optional[torch.Tensor] = None, stable_softmax: bool = False) -> torch.Tensor:
+        """Forward one sample (``nn_run_kernel`` inner step); returns the output vector (device)."""
+        if t is None:
+            self.target_buf.zero_()
+        self.load_sample(x, t)
+        o = self.make_opts(N.TRAIN_BP, stable_softmax=stable_softmax)
+        N.check(self.lib.hpnn_dev_train_sample(C.byref(self.net), C.byref(o), 1, self._res_dev.data_ptr(),
+                                               self._stream()), "hpnn_dev_train_sample(run)")
+        return self.output_buf
+
+    # ------------------------------------------------------------------ batched inference
+    def forward_batch(self, X: torch.Tensor, stable_softmax: bool = False, precision: str = "fp64") -> torch.Tensor:
+        """``[B, n_in] -> [B, n_out]`` (extension).  Single rank only; a row-split
+        job gathers each layer with one collective per layer in
+        :func:`hpnn_b200.parallel.tp.forward_batch_tp`."""
+        from ..ops import cuda as ops
+
+        if self.world != 1:
+            raise RuntimeError("forward_batch on a row-split net: use parallel.tp.forward_batch_tp")
+        H = X.to(self.device, torch.float64).contiguous()
+        NL = self.n_layers
+        for l in range(NL):
+            last = l == NL - 1
+            kind = 1 if (last and self.type == N.TYPE_SNN) else 0
+            H = ops.forward_batch(self.W_full[l], self.dims[l], H, kind, precision=precision)
+        if self.type == N.TYPE_SNN:
+            ops.softmax_rows_(H, stable_softmax)
+        return H
+
+    # ------------------------------------------------------------------ export
+    def local_kernel_rows(self) -> List[np.ndarray]:
+        torch.cuda.synchronize(self.device)
+        return [w.detach().cpu().numpy().copy() for w in self.weights]
+
+    def to_kernel(self) -> Kernel:
+        """Gather the row slices of all ranks into a host ``Kernel`` (every rank gets it)."""
+        rows = self.local_kernel_rows()
+        if self.world == 1:
+            return Kernel(list(self.dims), rows, self.name)
+        import torch.distributed as dist
+
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, rows, group=self.group)
+        ws = [np.concatenate([everyone[g][l] for g in range(self.world)], axis=0) for l in range(self.n_layers)]
+        return Kernel(list(self.dims), ws, self.name)
+
+    def load_weights(self, kernel: Kernel) -> None:
+        for l, W in enumerate(self.W_full):
+            r0 = self.net.row0[l]
+            src = torch.from_numpy(np.ascontiguousarray(kernel.weights[l][r0:r0 + self.net.rows[l]]))
+            W[:, : self.dims[l]].copy_(src)

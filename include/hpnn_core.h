@@ -1,0 +1,223 @@
+/*
+ * hpnn_core.h -- C ABI of the hpnn-b200 native core (libhpnn_core.so).
+ *
+ * The core is libtorch-free: it owns the file formats, the CPU/OpenMP oracle
+ * and every sm_100a kernel.  Three users sit on top of it:
+ *   - the PyTorch framework layer (hpnn_b200/, via ctypes: tensors are passed
+ *     as raw device pointers, launches go to the caller's CUDA stream),
+ *   - the libhpnn.h compatibility shim (csrc/capi/libhpnn.cpp),
+ *   - plain C/C++ host programs.
+ *
+ * Reference parity notes cite /root/reference paths as file:line.
+ */
+#ifndef HPNN_CORE_H
+#define HPNN_CORE_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HPNN_MAX_LAYERS 16 /* weight layers (hidden layers + output layer)   */
+#define HPNN_MAX_WORLD 8   /* ranks (GPUs) in one NVLink domain              */
+#define HPNN_TINY 1E-14    /* include/libhpnn/common.h:79                    */
+
+/* network type / trainer: same numeric values as include/libhpnn.h:51-66 */
+enum { HPNN_TYPE_ANN = 0, HPNN_TYPE_LNN = 1, HPNN_TYPE_SNN = 2, HPNN_TYPE_UKN = -1 };
+enum { HPNN_TRAIN_BP = 0, HPNN_TRAIN_BPM = 1, HPNN_TRAIN_CG = 2, HPNN_TRAIN_SPLX = 3, HPNN_TRAIN_UKN = -1 };
+
+/* ------------------------------------------------------------------------ */
+/* host-side network ("kernel" in libhpnn parlance): topology + fp64 weights */
+/* ------------------------------------------------------------------------ */
+typedef struct hpnn_kernel hpnn_kernel;
+
+/* dims = {n_in, h_1, ..., h_K, n_out}; n_dims = K+2; weights zeroed. */
+hpnn_kernel *hpnn_kernel_create(int n_dims, const int *dims);
+void hpnn_kernel_destroy(hpnn_kernel *k);
+int hpnn_kernel_n_layers(const hpnn_kernel *k);      /* weight layers = n_dims-1 */
+int hpnn_kernel_dim(const hpnn_kernel *k, int i);    /* i in [0, n_layers]       */
+double *hpnn_kernel_weights(hpnn_kernel *k, int l);  /* row-major [dim(l+1) x dim(l)] */
+const char *hpnn_kernel_name(const hpnn_kernel *k);  /* NULL if unnamed          */
+void hpnn_kernel_set_name(hpnn_kernel *k, const char *name);
+/* glibc srandom/random init, 2(r-0.5)/sqrt(fan_in), layer by layer, row-major
+ * (src/ann.c:632-703).  *seed==0 -> time(NULL), written back. */
+hpnn_kernel *hpnn_kernel_generate(unsigned *seed, int n_dims, const int *dims);
+hpnn_kernel *hpnn_kernel_load(const char *path);            /* src/ann.c:206-631 */
+int hpnn_kernel_dump(const hpnn_kernel *k, FILE *fp);       /* src/ann.c:770-857 */
+int hpnn_kernel_dump_path(const hpnn_kernel *k, const char *path);
+/* exact fp64 sidecar (the text format loses bits) */
+int hpnn_kernel_dump_binary(const hpnn_kernel *k, const char *path);
+hpnn_kernel *hpnn_kernel_load_binary(const char *path);
+
+/* ------------------------------------------------------------------------ */
+/* nn.conf (src/libhpnn.c:658-937)                                           */
+/* ------------------------------------------------------------------------ */
+typedef struct {
+  char *name;
+  int type;       /* HPNN_TYPE_*  */
+  int need_init;  /* [init] generate */
+  unsigned seed;
+  char *f_kernel; /* [init] <file>  */
+  int train;      /* HPNN_TRAIN_* */
+  char *samples;
+  char *tests;
+  int n_in, n_out, n_hid;
+  int *hid;
+} hpnn_conf;
+
+/* returns 0 on success; strings/arrays are malloc'd, release with _free */
+int hpnn_conf_load(const char *path, hpnn_conf *out);
+void hpnn_conf_free(hpnn_conf *c);
+/* writer of src/libhpnn.c:885-937; dims may be NULL (sizes printed as 0) */
+int hpnn_conf_dump(const hpnn_conf *c, int n_dims, const int *dims, FILE *fp);
+
+/* ------------------------------------------------------------------------ */
+/* samples and directory walks (src/libhpnn.c:1070-1145, 1184-1229)          */
+/* ------------------------------------------------------------------------ */
+/* *in / *out are malloc'd (free with hpnn_free); returns 0 on success */
+int hpnn_sample_read(const char *path, double **in, int *n_in, double **out, int *n_out);
+int hpnn_sample_write(const char *path, const double *in, int n_in, const double *out, int n_out,
+                      const char *comment);
+/* readdir() order, dot-files skipped; names is a malloc'd array of malloc'd strings */
+int hpnn_dir_list(const char *dir, char ***names, int *n);
+void hpnn_dir_list_free(char **names, int n);
+/* the reference's srandom(seed) + rejection draw without replacement */
+void hpnn_shuffle_order(unsigned seed, int n, int *order);
+void hpnn_free(void *p);
+
+/* ------------------------------------------------------------------------ */
+/* CPU / OpenMP engine: fallback and test oracle (src/ann.c, src/snn.c)      */
+/* ------------------------------------------------------------------------ */
+typedef struct {
+  double init_err;  /* error of the first forward ("init=")                 */
+  double final_de;  /* last E_before - E_after ("final=")                   */
+  double last_err;  /* error after the last iteration                       */
+  int n_iter;       /* N_ITER                                               */
+  int first_ok;     /* argmax matched the target after iteration 1 (OK/NO)  */
+  int success;      /* loop-exit is_ok (SUCCESS!/FAIL!)                      */
+  int reserved;
+} hpnn_train_result;
+
+typedef struct {
+  int type;        /* HPNN_TYPE_ANN | HPNN_TYPE_SNN                          */
+  int train;       /* HPNN_TRAIN_BP | HPNN_TRAIN_BPM                         */
+  double lr;       /* <=0 -> backend default                                 */
+  double alpha;    /* momentum factor (BPM), reference passes 0.2            */
+  double delta;    /* <=0 -> 1e-6                                            */
+  int min_iter;    /* <0 -> 31 (BP) / 15 (BPM)                               */
+  int max_iter;    /* <0 -> 102399                                           */
+  int stable_softmax; /* 0 = reference formula exp(z-1) (parity), 1 = max-shifted */
+} hpnn_train_opts;
+
+void hpnn_train_opts_default(hpnn_train_opts *o, int type, int train, int cuda_defaults);
+void hpnn_set_omp_threads(int n);
+/* out must hold dim(n_layers) doubles */
+int hpnn_cpu_forward(const hpnn_kernel *k, int type, int stable_softmax, const double *in, double *out);
+/* one BP/BPM iteration on a forwarded net is not exposed: the per-sample loop is */
+int hpnn_cpu_train_sample(hpnn_kernel *k, const hpnn_train_opts *o, const double *in,
+                          const double *target, hpnn_train_result *res, double *out);
+
+/* ------------------------------------------------------------------------ */
+/* device engine (sm_100a)                                                   */
+/* ------------------------------------------------------------------------ */
+/* All pointers are device pointers owned by the caller.  W rows are stored with
+ * a padded leading dimension ld[l] (multiple of 8 doubles, pad = 0) so that
+ * every row is 64-byte aligned.  In a row-split (tensor-parallel) job each
+ * rank holds rows [row0[l], row0[l]+rows[l]) of every layer.  The "arena" is a
+ * per-rank buffer with the SAME layout on every rank; arena[p] is rank p's
+ * arena as mapped into this process (peer memory), arena[rank] the local one. */
+typedef struct {
+  int n_layers;
+  int dims[HPNN_MAX_LAYERS + 1];
+  int ld[HPNN_MAX_LAYERS];      /* leading dim of W[l], >= dims[l]          */
+  int row0[HPNN_MAX_LAYERS];
+  int rows[HPNN_MAX_LAYERS];
+  double *W[HPNN_MAX_LAYERS];   /* [rows[l] x ld[l]]                        */
+  double *dW[HPNN_MAX_LAYERS];  /* momentum, same shape, or NULL            */
+  int rank, world;
+  double *arena[HPNN_MAX_WORLD];
+  unsigned *local_sync;         /* 64 zeroed u32 words, private to the rank  */
+  /* arena layout (offsets in doubles), filled by hpnn_dev_arena_layout      */
+  long long off_act[HPNN_MAX_LAYERS + 1]; /* act[0]=input, act[l+1]=out of l */
+  long long off_part[HPNN_MAX_LAYERS];    /* per-rank partial W^T.delta      */
+  long long off_target;
+  long long off_out;                      /* final output vector             */
+  long long off_flags;                    /* cross-rank barrier flags        */
+  long long arena_doubles;                /* total size                      */
+  int part_stride[HPNN_MAX_LAYERS];       /* max owned rows of layer l       */
+} hpnn_dev_net;
+
+/* fills ld/row0/rows/offsets from dims/rank/world; returns arena size in doubles */
+long long hpnn_dev_arena_layout(hpnn_dev_net *net);
+
+/* plain device memory helpers (cudaMalloc/cudaFree, zero-filled) + CUDA IPC */
+int hpnn_cuda_device_count(void);
+int hpnn_cuda_set_device(int dev);
+void *hpnn_dev_alloc(size_t bytes);
+void hpnn_dev_free(void *p);
+int hpnn_dev_memset(void *p, int v, size_t bytes, void *stream);
+int hpnn_dev_h2d(void *dst, const void *src, size_t bytes, void *stream);
+int hpnn_dev_d2h(void *dst, const void *src, size_t bytes, void *stream);
+int hpnn_dev_sync(void *stream);
+void *hpnn_host_alloc_pinned(size_t bytes);
+void hpnn_host_free_pinned(void *p);
+int hpnn_ipc_export(void *dev_ptr, unsigned char handle[64]);
+void *hpnn_ipc_open(const unsigned char handle[64]);
+int hpnn_ipc_close(void *p);
+int hpnn_enable_peer_access(int dev, int peer);
+const char *hpnn_last_error(void);
+
+/* persistent per-sample kernel (K-P).  Input must already be in act[0] and the
+ * target in off_target of the LOCAL arena (every rank loads the same sample).
+ * result is a device pointer.  mode 0: train to convergence, 1: forward only
+ * (the softmaxed / activated output lands at off_out).  Returns 0 on success. */
+int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
+                          hpnn_train_result *result_dev, void *stream);
+/* number of co-resident CTAs the persistent kernel will use on this device */
+int hpnn_dev_persistent_grid(void);
+/* set grid (CTAs) used by K-P: 0 = one per SM (default) */
+void hpnn_dev_set_persistent_grid(int ctas);
+
+/* stand-alone phase kernels (K-A..K-E), one launch each, single rank or one
+ * rank's slice.  Used by unit tests, by the multi-launch trainer and by the
+ * NCCL-collective baseline of the row split. */
+/* y[r] = f(W[r,:].x): act_kind 0 = 2/(1+e^-x)-1, 1 = identity               */
+int hpnn_dev_forward_layer(const double *W, int ld, int rows, int cols, const double *x, double *y,
+                           int act_kind, void *stream);
+/* output statistics: type ANN: o given; SNN: z given and o (softmax) written.
+ * delta_out[j] (j<n), stats[0]=E, stats[1]=argmax, stats[2]=target index     */
+int hpnn_dev_output_stats(int type, int stable_softmax, const double *z, const double *target, int n,
+                          double *o, double *delta_out, double *stats, void *stream);
+/* part[c] = sum_r W[r,c]*delta[r] (old W), then optionally the BP/BPM update
+ * W[r,c] += lr*delta[r]*h[c] in the same pass.  update: 0 none, 1 BP, 2 BPM   */
+int hpnn_dev_backward_update(double *W, double *dW, int ld, int rows, int cols, const double *delta,
+                             const double *h, double *part, int update, double lr, double alpha,
+                             void *stream);
+/* delta[r] = dact(h[r]) * sum_g part[g*stride + r]                            */
+int hpnn_dev_delta_finalize(const double *part, int n_parts, int stride, const double *h, int n,
+                            double *delta, void *stream);
+/* first layer: W[r,:] += lr*delta[r]*x (or BPM triple), then y[r] = f(W[r,:].x) */
+int hpnn_dev_update_forward(double *W, double *dW, int ld, int rows, int cols, const double *delta,
+                            const double *x, double *y, int update, double lr, double alpha,
+                            int act_kind, void *stream);
+
+/* batched inference (extension): Y[B x N] = f(X[B x M] . W^T), fp64 */
+int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, const double *X, int ldx,
+                               int batch, double *Y, int ldy, int act_kind, void *stream);
+/* row-wise softmax exp(z-1)/(TINY+sum) on a [batch x n] matrix (in place) */
+int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void *stream);
+
+/* data-parallel gradient merge (extension): W += sum_ranks G_rank */
+int hpnn_dev_grad_merge(double *W, long long n, double *const *grads, int n_ranks, double scale,
+                        void *stream);
+
+/* launch counter: number of kernels this library launched since the last reset */
+long long hpnn_dev_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HPNN_CORE_H */
