@@ -1,0 +1,86 @@
+"""CPU/OpenMP engine vs the PyTorch specification and vs golden numbers recorded from the
+reference binary (gcc -O2 -fopenmp -D_OMP build of /root/reference, toy problem below)."""
+import numpy as np
+import pytest
+import torch
+
+import hpnn_b200 as hp
+from hpnn_b200 import _native as N
+from hpnn_b200.ops import reference as R
+from hpnn_b200.trainer import CpuEngine, TorchEngine
+
+from conftest import make_problem
+
+# reference train_nn output for: ANN 8-5-4-3, BP, seed 10958, samples = make_problem(ANN)
+# written with write_sample (%7.5f) and visited in this order
+REF_ORDER = [2, 4, 1, 0, 5, 3]
+REF_NITER = [31403, 24208, 9146, 25292, 18347, 21753]
+REF_INIT = [1.5139345432, 3.2261434563, 0.1447097800, 3.7106713300, 3.4675286205, 1.5578267625]
+
+
+def _rounded(X):
+    return np.array([[float("%7.5f" % v) for v in row] for row in X])
+
+
+def test_matches_reference_binary_golden():
+    k, _ = hp.generate_kernel(10958, 8, [5, 4], 3)
+    X, T = make_problem(N.TYPE_ANN)
+    X = _rounded(X)
+    eng = CpuEngine(k, N.TYPE_ANN, N.TRAIN_BP)
+    for j, i in enumerate(REF_ORDER):
+        r = eng.train(X[i], T[i])
+        assert r.n_iter == REF_NITER[j]
+        assert abs(r.init_err - REF_INIT[j]) < 1e-9
+        assert r.success and r.final_de <= 1e-6
+    eng.close()
+
+
+@pytest.mark.parametrize("nn_type,train", [(N.TYPE_ANN, N.TRAIN_BP), (N.TYPE_ANN, N.TRAIN_BPM),
+                                           (N.TYPE_SNN, N.TRAIN_BP), (N.TYPE_SNN, N.TRAIN_BPM)])
+def test_cpu_engine_equals_torch_spec(nn_type, train):
+    k, _ = hp.generate_kernel(77, 8, [6, 5], 3)
+    X, T = make_problem(nn_type, n_samples=2)
+    a = CpuEngine(k, nn_type, train, max_iter=300)
+    b = TorchEngine(k, nn_type, train, max_iter=300)
+    for x, t in zip(X, T):
+        ra, rb = a.train(x, t), b.train(x, t)
+        assert ra.n_iter == rb.n_iter and ra.first_ok == rb.first_ok and ra.success == rb.success
+        assert abs(ra.init_err - rb.init_err) < 1e-12 and abs(ra.final_de - rb.final_de) < 1e-12
+    for wa, wb in zip(a.kernel().weights, b.kernel().weights):
+        np.testing.assert_allclose(wa, wb, atol=1e-12)
+    np.testing.assert_allclose(a.run(X[0]), b.run(X[0]), atol=1e-13)
+    a.close()
+
+
+def test_default_learning_rates():
+    o = N.TrainOpts()
+    lib = N.load()
+    import ctypes as C
+    for (ty, tr, cuda), lr in {(N.TYPE_ANN, N.TRAIN_BP, 0): 0.001, (N.TYPE_ANN, N.TRAIN_BPM, 0): 0.0005,
+                               (N.TYPE_SNN, N.TRAIN_BP, 0): 0.01, (N.TYPE_ANN, N.TRAIN_BP, 1): 0.01,
+                               (N.TYPE_ANN, N.TRAIN_BPM, 1): 0.01}.items():
+        lib.hpnn_train_opts_default(C.byref(o), ty, tr, cuda)
+        assert o.lr == lr and o.alpha == 0.2 and o.delta == 1e-6 and o.max_iter == 102399
+        assert o.min_iter == (15 if tr == N.TRAIN_BPM else 31)
+
+
+def test_softmax_reference_formula_and_stable_mode():
+    z = torch.tensor([0.3, -1.2, 2.0], dtype=torch.float64)
+    o = R.softmax_ref(z)
+    e = torch.exp(z - 1.0)
+    torch.testing.assert_close(o, e / (e.sum() + 1e-14))
+    torch.testing.assert_close(R.softmax_ref(z, stable=True), torch.softmax(z, 0), atol=1e-13, rtol=0)
+    big = torch.tensor([800.0, 0.0], dtype=torch.float64)  # overflows without the max shift
+    assert not torch.isfinite(R.softmax_ref(big)).all()
+    assert torch.isfinite(R.softmax_ref(big, stable=True)).all()
+
+
+def test_loop_bounds_min_and_max_iter():
+    k, _ = hp.generate_kernel(5, 8, [5], 3)
+    X, T = make_problem(N.TYPE_ANN, n_samples=1)
+    e = CpuEngine(k, N.TYPE_ANN, N.TRAIN_BP, max_iter=10)
+    r = e.train(X[0], T[0])
+    assert r.n_iter == 11  # `if(iter>MAX) break` fires at MAX+1 (src/ann.c:2360)
+    e2 = CpuEngine(k, N.TYPE_ANN, N.TRAIN_BP, delta=1e9, min_iter=40)
+    r2 = e2.train(X[0], T[0])
+    assert r2.n_iter >= 41  # at least MIN+1 iterations even when dE is already small

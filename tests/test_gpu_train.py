@@ -1,0 +1,85 @@
+"""The persistent per-sample trainer (K-P) against the CPU engine (itself bit-identical to the
+reference binary, see test_cpu_engine.py) and the multi-launch path built from K-A..K-E."""
+import numpy as np
+import pytest
+import torch
+
+import hpnn_b200 as hp
+from hpnn_b200 import _native as N
+from hpnn_b200.trainer import CpuEngine, CudaEngine
+
+from conftest import make_problem
+
+pytestmark = pytest.mark.gpu
+
+CASES = [(N.TYPE_ANN, N.TRAIN_BP), (N.TYPE_ANN, N.TRAIN_BPM), (N.TYPE_SNN, N.TRAIN_BP), (N.TYPE_SNN, N.TRAIN_BPM)]
+
+
+@pytest.mark.parametrize("nn_type,train", CASES)
+@pytest.mark.parametrize("topo", [(8, (5, 4), 3), (64, (48,), 10), (100, (37, 29, 23), 7)])
+def test_persistent_trainer_matches_cpu_engine(nn_type, train, topo):
+    n_in, hid, n_out = topo
+    k, _ = hp.generate_kernel(4242, n_in, list(hid), n_out)
+    X, T = make_problem(nn_type, n_in, hid, n_out, n_samples=3, seed=5)
+    gpu = CudaEngine(k, nn_type, train, max_iter=2000)
+    cpu = CpuEngine(k, nn_type, train, max_iter=2000, cuda_defaults=True)
+    for x, t in zip(X, T):
+        rg, rc = gpu.train(x, t), cpu.train(x, t)
+        assert abs(rg.init_err - rc.init_err) < 1e-11
+        assert rg.first_ok == rc.first_ok and rg.success == rc.success
+        # different fp64 summation orders may move the exit by a few iterations
+        assert abs(rg.n_iter - rc.n_iter) <= max(3, rc.n_iter // 100)
+        if rg.n_iter == rc.n_iter:
+            assert abs(rg.final_de - rc.final_de) < 1e-10
+    wg, wc = gpu.kernel(), cpu.kernel()
+    for a, b in zip(wg.weights, wc.weights):
+        np.testing.assert_allclose(a, b, atol=1e-6)
+    np.testing.assert_allclose(gpu.run(X[0]), cpu.run(X[0]), atol=1e-6)
+    gpu.close()
+    cpu.close()
+
+
+@pytest.mark.parametrize("nn_type,train", CASES)
+def test_fixed_iteration_count_is_tight(nn_type, train):
+    """With min_iter == max_iter both engines do exactly the same number of iterations, so the
+    weights must agree to round-off (ChangeLog:33-38 asks for < 1e-12 between back-ends)."""
+    k, _ = hp.generate_kernel(99, 32, [24, 16], 5)
+    X, T = make_problem(nn_type, 32, (24, 16), 5, n_samples=2, seed=9)
+    kw = dict(max_iter=50, min_iter=60, delta=1e-300)
+    gpu = CudaEngine(k, nn_type, train, **kw)
+    cpu = CpuEngine(k, nn_type, train, cuda_defaults=True, **kw)
+    for x, t in zip(X, T):
+        rg, rc = gpu.train(x, t), cpu.train(x, t)
+        assert rg.n_iter == rc.n_iter == 51
+        assert abs(rg.last_err - rc.last_err) < 1e-12
+    for a, b in zip(gpu.kernel().weights, cpu.kernel().weights):
+        np.testing.assert_allclose(a, b, atol=1e-12)
+    gpu.close()
+    cpu.close()
+
+
+def test_run_only_and_pipelined_pass():
+    k, _ = hp.generate_kernel(7, 20, [16], 4)
+    X, T = make_problem(N.TYPE_SNN, 20, (16,), 4, n_samples=5, seed=3)
+    gpu = CudaEngine(k, N.TYPE_SNN, N.TRAIN_BPM, max_iter=300)
+    cpu = CpuEngine(k, N.TYPE_SNN, N.TRAIN_BPM, max_iter=300, cuda_defaults=True)
+    np.testing.assert_allclose(gpu.run(X[0]), cpu.run(X[0]), atol=1e-13)
+    Xp, Tp = torch.from_numpy(X).pin_memory(), torch.from_numpy(T).pin_memory()
+    res = gpu.train_many(Xp, Tp)
+    ref = [cpu.train(x, t) for x, t in zip(X, T)]
+    assert [abs(a.n_iter - b.n_iter) <= 3 for a, b in zip(res, ref)] == [True] * 5
+    for a, b in zip(gpu.kernel().weights, cpu.kernel().weights):
+        np.testing.assert_allclose(a, b, atol=1e-6)
+    gpu.close()
+
+
+def test_native_library_is_the_one_in_tree():
+    from hpnn_b200.ops import cuda as ops
+
+    assert N.lib_path().exists() and "hpnn_b200/lib" in str(N.lib_path())
+    before = ops.launch_count()
+    k, _ = hp.generate_kernel(7, 20, [16], 4)
+    gpu = CudaEngine(k, N.TYPE_ANN, N.TRAIN_BP, max_iter=5)
+    gpu.train(np.zeros(20), np.array([1.0, -1, -1, -1]))
+    assert ops.launch_count() == before + 1  # one cooperative launch per sample
+    gpu.close()

@@ -1,0 +1,147 @@
+"""File formats, RNG parity and directory walk."""
+import io
+import os
+
+import numpy as np
+import pytest
+
+import hpnn_b200 as hp
+from hpnn_b200 import _native as N
+from hpnn_b200.config import dump_conf, parse_conf
+from hpnn_b200.kernel_io import dump_kernel_binary, load_kernel_binary
+from hpnn_b200.samples import list_dir
+
+from conftest import write_conf
+
+# first weights of `[seed] 10958`, 8-5-4-3, as written by the reference binary's kernel.tmp
+REF_FIRST_ROW = [-0.281305454478708, -0.027710347937003, -0.077296293698722, 0.154056015704165,
+                 0.042771657614647, -0.165060284230241, 0.024460498947952, 0.243725484355540]
+
+
+def test_generate_matches_reference_binary():
+    k, seed = hp.generate_kernel(10958, 8, [5, 4], 3)
+    assert seed == 10958 and k.dims == [8, 5, 4, 3] and k.name is None
+    np.testing.assert_allclose(k.weights[0][0], REF_FIRST_ROW, atol=5e-16)
+    for l, w in enumerate(k.weights):  # |w| <= 1/sqrt(fan_in)
+        assert np.abs(w).max() <= 1.0 / np.sqrt(k.dims[l]) + 1e-15
+
+
+def test_seed_zero_uses_time():
+    _, seed = hp.generate_kernel(0, 4, [3], 2)
+    assert seed != 0
+
+
+def test_shuffle_is_glibc_random():
+    assert hp.shuffle_order(10958, 8) == [0, 3, 5, 4, 2, 6, 1, 7]
+    assert sorted(hp.shuffle_order(1, 100)) == list(range(100))
+
+
+def test_kernel_text_roundtrip(tmp_path):
+    k, _ = hp.generate_kernel(42, 7, [6, 5], 4)
+    p = tmp_path / "kernel.tmp"
+    hp.dump_kernel(k, str(p))
+    text = p.read_text().splitlines()
+    assert text[0] == "[name] (null)"  # generated kernels are unnamed
+    assert text[1] == "[param] 7 6 5 4" and text[2] == "[input] 7" and text[3] == "[hidden 1] 6"
+    assert text[4] == "[neuron 1] 7"
+    assert all(len(tok.split(".")[1]) == 15 for tok in text[5].split())
+    k2 = hp.load_kernel(str(p))
+    assert k2.dims == k.dims and k2.name == "(null)"
+    for a, b in zip(k.weights, k2.weights):
+        np.testing.assert_allclose(a, b, atol=1e-15)
+    # dump of the reloaded kernel is byte-identical except for nothing: name line equal too
+    p2 = tmp_path / "kernel2"
+    hp.dump_kernel(k2, str(p2))
+    assert p2.read_text() == p.read_text()
+
+
+def test_kernel_binary_sidecar_is_exact(tmp_path):
+    k, _ = hp.generate_kernel(5, 9, [4], 3)
+    k.name = "exact"
+    dump_kernel_binary(k, str(tmp_path / "k.bin"))
+    k2 = load_kernel_binary(str(tmp_path / "k.bin"))
+    assert k2.name == "exact" and all((a == b).all() for a, b in zip(k.weights, k2.weights))
+
+
+def test_kernel_load_errors(tmp_path):
+    p = tmp_path / "bad"
+    p.write_text("[nope]\n")
+    with pytest.raises(IOError):
+        hp.load_kernel(str(p))
+    p.write_text("[name] x\n[param] 3 0 2\n")
+    with pytest.raises(IOError):
+        hp.load_kernel(str(p))
+    with pytest.raises(IOError):
+        hp.load_kernel(str(tmp_path / "missing"))
+
+
+def test_conf_parse_and_dump(tmp_path):
+    c = tmp_path / "nn.conf"
+    write_conf(c, nn_type="SNN", train="BPM", hid="30 20 10", n_in=12, n_out=5, samples="/a/b  # comment")
+    conf = parse_conf(str(c))
+    assert conf.name == "toy" and conf.type == N.TYPE_SNN and conf.train == N.TRAIN_BPM
+    assert conf.need_init and conf.seed == 10958 and conf.n_inputs == 12 and conf.hiddens == [30, 20, 10]
+    assert conf.n_outputs == 5 and conf.samples == "/a/b" and conf.tests == "./tests"
+    text = dump_conf(conf)
+    assert "[type] SNN" in text and "[train] BPM" in text and "[hiddens] 30 20 10 " in text
+    # the dumped form ([inputs]/[hiddens]/[outputs]) is accepted back
+    c2 = tmp_path / "nn2.conf"
+    c2.write_text(text)
+    conf2 = parse_conf(str(c2))
+    assert conf2.hiddens == [30, 20, 10] and conf2.n_inputs == 12 and conf2.n_outputs == 5
+
+
+@pytest.mark.parametrize("train,expect", [("BP", N.TRAIN_BP), ("BPM", N.TRAIN_BPM), ("CG", N.TRAIN_CG),
+                                          ("SPLX", N.TRAIN_SPLX), ("zzz", N.TRAIN_UKN)])
+def test_conf_train_keywords(tmp_path, train, expect):
+    c = tmp_path / "nn.conf"
+    write_conf(c, train=train)
+    assert parse_conf(str(c)).train == expect
+
+
+def test_conf_errors(tmp_path):
+    c = tmp_path / "nn.conf"
+    c.write_text("# nothing\n[name] x\n")
+    with pytest.raises(ValueError):
+        parse_conf(str(c))  # missing [type]
+    write_conf(c, hid="5 0")
+    with pytest.raises(ValueError):
+        parse_conf(str(c))
+    c.write_text("#\n[type] ANN\n[init] generate\n[hidden] 3\n[output] 2\n")
+    with pytest.raises(ValueError):
+        parse_conf(str(c))  # missing [input]
+    with pytest.raises(ValueError):
+        parse_conf(str(tmp_path / "nope.conf"))
+
+
+def test_conf_init_from_file(tmp_path):
+    k, _ = hp.generate_kernel(3, 8, [5, 4], 3)
+    hp.dump_kernel(k, str(tmp_path / "kernel.opt"))
+    c = tmp_path / "nn.conf"
+    write_conf(c, init=str(tmp_path / "kernel.opt"))
+    conf = hp.load_conf(str(c))
+    assert not conf.need_init and conf.kernel.dims == [8, 5, 4, 3]
+
+
+def test_sample_roundtrip_and_comment(tmp_path):
+    x = np.array([0.5, 255.0, 0.12345678, 3.0])
+    t = np.array([-1.0, 1.0, -1.0])
+    p = tmp_path / "s00001.txt"
+    hp.write_sample(str(p), x, t, "1")
+    lines = p.read_text().splitlines()
+    assert lines[0] == "[input] 4" and lines[2] == "[output] 3  #1" and lines[3] == "-1.0 1.0 -1.0"
+    assert lines[1] == "0.50000 255.00000 0.12346 3.00000"
+    x2, t2 = hp.read_sample(str(p))
+    np.testing.assert_allclose(x2, [0.5, 255.0, 0.12346, 3.0])
+    np.testing.assert_array_equal(t2, t)
+    with pytest.raises(IOError):
+        hp.read_sample(str(tmp_path / "missing.txt"))
+
+
+def test_dir_walk_skips_dotfiles_and_covers_all(toy_dir):
+    (toy_dir / "samples" / ".hidden").write_text("x")
+    names = list_dir(str(toy_dir / "samples"))
+    assert ".hidden" not in names and sorted(names) == [f"s{i:03d}.txt" for i in range(6)]
+    files = hp.walk(str(toy_dir / "samples"), 10958)
+    assert sorted(os.path.basename(f) for f in files) == sorted(names)
+    assert files == hp.walk(str(toy_dir / "samples"), 10958)  # deterministic for a seed
