@@ -1,0 +1,87 @@
+"""Multi-GPU check of the fused row-split trainer; run under torchrun, one rank per GPU:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29511 tests/mp_tp_check.py
+
+Every rank trains the same samples with K-P over NVLink peer stores; rank 0 compares N_ITER,
+errors and the gathered weights with the CPU engine, and with the NCCL-collective baseline."""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import hpnn_b200 as hp  # noqa: E402
+from hpnn_b200 import _native as N  # noqa: E402
+from hpnn_b200.parallel.dist import init_world  # noqa: E402
+from hpnn_b200.parallel.tp_collective import CollectiveTPEngine  # noqa: E402
+from hpnn_b200.trainer import CpuEngine, CudaEngine  # noqa: E402
+
+
+def problem(nn_type, n_in, n_out, n, seed):
+    rng = np.random.default_rng(seed)
+    lo = 0.0 if nn_type == N.TYPE_SNN else -1.0
+    X = rng.random((n, n_in))
+    T = np.full((n, n_out), lo)
+    for i in range(n):
+        T[i, int(rng.integers(n_out))] = 1.0
+    return X, T
+
+
+def main():
+    group = init_world("nccl")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    fails = 0
+    cases = [(N.TYPE_ANN, N.TRAIN_BP, 64, [48, 40], 10), (N.TYPE_SNN, N.TRAIN_BPM, 100, [37, 29, 23], 7),
+             (N.TYPE_SNN, N.TRAIN_BPM, 784, [300, 200], 10), (N.TYPE_ANN, N.TRAIN_BPM, 33, [5], 3)]
+    for nn_type, train, n_in, hid, n_out in cases:
+        k, _ = hp.generate_kernel(77, n_in, hid, n_out)
+        X, T = problem(nn_type, n_in, n_out, 3, 11)
+        kw = dict(max_iter=400)
+        fused = CudaEngine(k, nn_type, train, group=group, **kw)
+        coll = CollectiveTPEngine(k, nn_type, train, group=group, device=f"cuda:{torch.cuda.current_device()}", **kw)
+        cpu = CpuEngine(k, nn_type, train, cuda_defaults=True, **kw) if rank == 0 else None
+        t_f = t_c = 0.0
+        for x, t in zip(X, T):
+            torch.cuda.synchronize(); dist.barrier(); t0 = time.perf_counter()
+            rf = fused.train(x, t)
+            torch.cuda.synchronize(); t_f += time.perf_counter() - t0
+            dist.barrier(); t0 = time.perf_counter()
+            rc = coll.train(x, t)
+            torch.cuda.synchronize(); t_c += time.perf_counter() - t0
+            if rank == 0:
+                r0 = cpu.train(x, t)
+                ok = (abs(rf.n_iter - r0.n_iter) <= max(3, r0.n_iter // 100) and abs(rf.init_err - r0.init_err) < 1e-11
+                      and rf.first_ok == r0.first_ok and rf.success == r0.success
+                      and abs(rc.n_iter - r0.n_iter) <= max(3, r0.n_iter // 100))
+                if not ok:
+                    fails += 1
+                    print(f"MISMATCH type={nn_type} train={train}: fused={rf} coll={rc} cpu={r0}", flush=True)
+        kf, kc = fused.kernel(), coll.kernel()
+        of = fused.run(X[0])
+        if rank == 0:
+            k0 = cpu.kernel()
+            e_f = max(float(np.abs(a - b).max()) for a, b in zip(kf.weights, k0.weights))
+            e_c = max(float(np.abs(a - b).max()) for a, b in zip(kc.weights, k0.weights))
+            e_o = float(np.abs(of - cpu.run(X[0])).max())
+            print(f"case type={nn_type} train={train} {n_in}-{hid}-{n_out} world={world}: max|dW| fused={e_f:.2e} "
+                  f"collective={e_c:.2e} max|do|={e_o:.2e}  time fused={t_f * 1e3:.1f} ms collective={t_c * 1e3:.1f} ms",
+                  flush=True)
+            if not (e_f < 1e-6 and e_c < 1e-6 and e_o < 1e-6):
+                fails += 1
+        fused.close()
+    flag = torch.tensor([fails], device="cuda")
+    dist.all_reduce(flag)
+    if rank == 0:
+        print("TP_CHECK_OK" if int(flag.item()) == 0 else "TP_CHECK_FAILED", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) == 0 else 1)
+
+
+if __name__ == "__main__":
+    main()
