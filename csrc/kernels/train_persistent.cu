@@ -52,7 +52,9 @@ struct Barrier {
       if (old == gridDim.x - 1) {
         *count = 0;  // nobody can arrive again before the release below
         if (n.world > 1) {
-          const unsigned long long we = (unsigned long long)(++(*wepoch));
+          const unsigned wnext = ld_acquire_gpu(wepoch) + 1u;
+          st_release_gpu(wepoch, wnext);
+          const unsigned long long we = (unsigned long long)wnext;
           fence_sys();
           for (int q = 0; q < n.world; ++q) {
             if (q == n.rank) continue;
