@@ -30,6 +30,9 @@ __device__ __forceinline__ unsigned atom_add_acqrel_gpu(unsigned *p, unsigned v)
   asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
   return old;
 }
+__device__ __forceinline__ void red_add_release_gpu(unsigned *p, unsigned v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
   unsigned long long v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -37,6 +40,19 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 }
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_relaxed_gpu(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
@@ -144,64 +160,64 @@ struct Dst {
 // xs: input vector in shared memory (ld doubles, pad = 0); ds: local deltas.
 // ---------------------------------------------------------------------------
 template <int UPD>
+__device__ __forceinline__ void row_apply(double2 &w, double2 &m, const double2 x, double s, double alpha,
+                                          double2 *wp, double2 *mp, double &a) {
+  if (UPD == 1) {
+    w.x = fma(s, x.x, w.x);
+    w.y = fma(s, x.y, w.y);
+    stg_cg2(wp, w);
+  } else if (UPD == 2) {
+    m.x = fma(s, x.x, m.x);
+    m.y = fma(s, x.y, m.y);
+    w.x += m.x;
+    w.y += m.y;
+    stg_cg2(wp, w);
+    m.x *= alpha;
+    m.y *= alpha;
+    stg_cg2(mp, m);
+  }
+  a = fma(w.x, x.x, a);
+  a = fma(w.y, x.y, a);
+}
+
+// One warp, one row.  The row is walked in chunks of 4 x 32 double2; the loads of chunk
+// k+1 are issued before chunk k is consumed, so a 1000-wide row costs ~one L2 round trip
+// instead of one per chunk (the small nets are latency bound) and a wide
+// row keeps 8 x 512 B per warp in flight.
+template <int UPD>
 __device__ __forceinline__ double warp_row(double *wrow, double *mrow, const double *xs, int ld, double s,
                                            double alpha, int lane) {
   double2 *w2 = reinterpret_cast<double2 *>(wrow);
   double2 *m2 = reinterpret_cast<double2 *>(mrow);
   const double2 *x2 = reinterpret_cast<const double2 *>(xs);
   const int n2 = ld >> 1;
+  const double2 zero2 = make_double2(0.0, 0.0);
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-  int i = lane;
-  for (; i + 96 < n2; i += 128) {
-    double2 w[4], m[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) w[u] = ldg_cg2(w2 + i + 32 * u);
-    if (UPD == 2) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u) m[u] = ldg_cg2(m2 + i + 32 * u);
-    }
+  double2 wa[4], ma[4], wb[4], mb[4];
+  auto load = [&](double2 (&w)[4], double2 (&m)[4], int base) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const double2 x = x2[i + 32 * u];
-      if (UPD == 1) {
-        w[u].x = fma(s, x.x, w[u].x);
-        w[u].y = fma(s, x.y, w[u].y);
-        stg_cg2(w2 + i + 32 * u, w[u]);
-      } else if (UPD == 2) {
-        m[u].x = fma(s, x.x, m[u].x);
-        m[u].y = fma(s, x.y, m[u].y);
-        w[u].x += m[u].x;
-        w[u].y += m[u].y;
-        stg_cg2(w2 + i + 32 * u, w[u]);
-        m[u].x *= alpha;
-        m[u].y *= alpha;
-        stg_cg2(m2 + i + 32 * u, m[u]);
+      const int i = base + lane + 32 * u;
+      w[u] = (i < n2) ? ldg_cg2(w2 + i) : zero2;
+      if (UPD == 2) m[u] = (i < n2) ? ldg_cg2(m2 + i) : zero2;
+    }
+  };
+  auto consume = [&](double2 (&w)[4], double2 (&m)[4], int base) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = base + lane + 32 * u;
+      if (i < n2) {
+        double &a = (u == 0) ? a0 : (u == 1) ? a1 : (u == 2) ? a2 : a3;
+        row_apply<UPD>(w[u], m[u], x2[i], s, alpha, w2 + i, m2 + i, a);
       }
-      double &a = (u == 0) ? a0 : (u == 1) ? a1 : (u == 2) ? a2 : a3;
-      a = fma(w[u].x, x.x, a);
-      a = fma(w[u].y, x.y, a);
     }
-  }
-  for (; i < n2; i += 32) {
-    double2 w = ldg_cg2(w2 + i);
-    const double2 x = x2[i];
-    if (UPD == 1) {
-      w.x = fma(s, x.x, w.x);
-      w.y = fma(s, x.y, w.y);
-      stg_cg2(w2 + i, w);
-    } else if (UPD == 2) {
-      double2 m = ldg_cg2(m2 + i);
-      m.x = fma(s, x.x, m.x);
-      m.y = fma(s, x.y, m.y);
-      w.x += m.x;
-      w.y += m.y;
-      stg_cg2(w2 + i, w);
-      m.x *= alpha;
-      m.y *= alpha;
-      stg_cg2(m2 + i, m);
-    }
-    a0 = fma(w.x, x.x, a0);
-    a0 = fma(w.y, x.y, a0);
+  };
+  load(wa, ma, 0);
+  for (int base = 0; base < n2; base += 256) {
+    load(wb, mb, base + 128);
+    consume(wa, ma, base);
+    load(wa, ma, base + 256);
+    consume(wb, mb, base + 128);
   }
   double a = (a0 + a1) + (a2 + a3);
 #pragma unroll
@@ -250,60 +266,50 @@ __device__ __forceinline__ void col_task(double *W, double *dW, int ld, int rows
   const size_t stride2 = (size_t)(ld >> 1);
   double2 *Wp = reinterpret_cast<double2 *>(W + c);
   double2 *Mp = reinterpret_cast<double2 *>((UPD == 2 ? dW : W) + c);
-  int r = rl;
-  for (; r + 3 * RL < rows; r += 4 * RL) {
-    double2 w[4], m[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) w[u] = ldg_cg2(Wp + (size_t)(r + u * RL) * stride2);
-    if (UPD == 2) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u) m[u] = ldg_cg2(Mp + (size_t)(r + u * RL) * stride2);
-    }
+  const double2 zero2 = make_double2(0.0, 0.0);
+  double2 wa[4], ma[4], wb[4], mb[4];
+  auto load = [&](double2 (&w)[4], double2 (&m)[4], int r0) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const double d = ds[r + u * RL];
-      a0 = fma(w[u].x, d, a0);
-      a1 = fma(w[u].y, d, a1);
-      if (UPD == 1) {
-        const double s = lr * d;
-        w[u].x = fma(s, h0, w[u].x);
-        w[u].y = fma(s, h1, w[u].y);
-        stg_cg2(Wp + (size_t)(r + u * RL) * stride2, w[u]);
-      } else if (UPD == 2) {
-        const double s = lr * d;
-        m[u].x = fma(s, h0, m[u].x);
-        m[u].y = fma(s, h1, m[u].y);
-        w[u].x += m[u].x;
-        w[u].y += m[u].y;
-        stg_cg2(Wp + (size_t)(r + u * RL) * stride2, w[u]);
-        m[u].x *= alpha;
-        m[u].y *= alpha;
-        stg_cg2(Mp + (size_t)(r + u * RL) * stride2, m[u]);
+      const int r = r0 + u * RL;
+      w[u] = (r < rows) ? ldg_cg2(Wp + (size_t)r * stride2) : zero2;
+      if (UPD == 2) m[u] = (r < rows) ? ldg_cg2(Mp + (size_t)r * stride2) : zero2;
+    }
+  };
+  auto consume = [&](double2 (&w)[4], double2 (&m)[4], int r0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + u * RL;
+      if (r < rows) {
+        const double d = ds[r];
+        a0 = fma(w[u].x, d, a0);
+        a1 = fma(w[u].y, d, a1);
+        if (UPD == 1) {
+          const double s = lr * d;
+          w[u].x = fma(s, h0, w[u].x);
+          w[u].y = fma(s, h1, w[u].y);
+          stg_cg2(Wp + (size_t)r * stride2, w[u]);
+        } else if (UPD == 2) {
+          const double s = lr * d;
+          m[u].x = fma(s, h0, m[u].x);
+          m[u].y = fma(s, h1, m[u].y);
+          w[u].x += m[u].x;
+          w[u].y += m[u].y;
+          stg_cg2(Wp + (size_t)r * stride2, w[u]);
+          m[u].x *= alpha;
+          m[u].y *= alpha;
+          stg_cg2(Mp + (size_t)r * stride2, m[u]);
+        }
       }
     }
-  }
-  for (; r < rows; r += RL) {
-    double2 w = ldg_cg2(Wp + (size_t)r * stride2);
-    const double d = ds[r];
-    a0 = fma(w.x, d, a0);
-    a1 = fma(w.y, d, a1);
-    if (UPD == 1) {
-      const double s = lr * d;
-      w.x = fma(s, h0, w.x);
-      w.y = fma(s, h1, w.y);
-      stg_cg2(Wp + (size_t)r * stride2, w);
-    } else if (UPD == 2) {
-      double2 m = ldg_cg2(Mp + (size_t)r * stride2);
-      const double s = lr * d;
-      m.x = fma(s, h0, m.x);
-      m.y = fma(s, h1, m.y);
-      w.x += m.x;
-      w.y += m.y;
-      stg_cg2(Wp + (size_t)r * stride2, w);
-      m.x *= alpha;
-      m.y *= alpha;
-      stg_cg2(Mp + (size_t)r * stride2, m);
-    }
+  };
+  // two batches of 4 rows in flight per thread (software pipeline, see warp_row)
+  load(wa, ma, rl);
+  for (int r0 = rl; r0 < rows; r0 += 8 * RL) {
+    load(wb, mb, r0 + 4 * RL);
+    consume(wa, ma, r0);
+    load(wa, ma, r0 + 8 * RL);
+    consume(wb, mb, r0 + 4 * RL);
   }
   // row lanes inside a warp share a column pair when lane % TPR matches
 #pragma unroll
@@ -360,9 +366,69 @@ struct OutStats {
 // z: gathered output (ANN: activated, SNN: raw).  For SNN the normalised output
 // is exp(z-1)/(TINY+sum) (src/snn.c:282-334) unless stable.  ds receives the
 // deltas of rows [row0,row0+rows) when non-null; o_out (global) the outputs.
+// Small output layers (n <= 32, the MNIST shape has 10): every warp evaluates the whole
+// vector redundantly with shuffles only, so the per-iteration evaluation costs one L2 round
+// trip and a single __syncthreads instead of ~10 block-wide reductions.
+__device__ __forceinline__ OutStats output_stats_small(int type, int stable, const double *z, const double *t,
+                                                       int n, int row0, int rows, double *ds, double *o_out) {
+  const int lane = threadIdx.x & 31;
+  const bool in = lane < n;
+  double o = in ? ldg_cg(z + lane) : 0.0;
+  const double tj = in ? ldg_cg(t + lane) : 0.0;
+  if (type == HPNN_TYPE_SNN) {
+    double shift = 1.0;
+    if (stable) {
+      double m = in ? o : -INFINITY;
+#pragma unroll
+      for (int k = 16; k; k >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, k));
+      shift = m;
+    }
+    const double e = in ? exp(o - shift) : 0.0;
+    double s = e;
+    // fixed order: sequential sum over lanes (matches the CPU engine's loop order)
+    double dv = HPNN_TINY;  // same order as the CPU engine: TINY + e_0 + e_1 + ...
+    for (int k = 0; k < n; ++k) dv += __shfl_sync(0xffffffffu, s, k);
+    o = e / dv;
+  }
+  double term, d;
+  if (type == HPNN_TYPE_SNN) {
+    term = (in && o > 0.) ? tj * log(o + HPNN_TINY) : 0.0;
+    d = tj - o;
+  } else {
+    term = in ? (tj - o) * (tj - o) : 0.0;
+    d = (tj - o) * dact_f(o);
+  }
+  double e = 0.0;
+  for (int k = 0; k < n; ++k) e += __shfl_sync(0xffffffffu, term, k);
+  double bv = (in && o == o) ? o : -INFINITY;
+  int bi = in ? lane : 0x7fffffff;
+  int trg = (in && tj == 1.0) ? lane : -1;
+#pragma unroll
+  for (int k = 16; k; k >>= 1) {
+    const double ov = __shfl_xor_sync(0xffffffffu, bv, k);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, k);
+    if (ov > bv || (ov == bv && oi < bi)) {
+      bv = ov;
+      bi = oi;
+    }
+    trg = max(trg, __shfl_xor_sync(0xffffffffu, trg, k));
+  }
+  if (threadIdx.x < 32 && in) {
+    if (ds && lane >= row0 && lane < row0 + rows) ds[lane - row0] = d;
+    if (o_out) stg_cg(o_out + lane, o);
+  }
+  OutStats st;
+  st.err = (type == HPNN_TYPE_SNN) ? e * (-1.0 / n) : 0.5 * e;
+  st.argmax = (bv > -1.0) ? bi : 0;
+  st.target = trg < 0 ? 0 : trg;
+  __syncthreads();
+  return st;
+}
+
 __device__ __forceinline__ OutStats output_stats(int type, int stable, const double *z, const double *t,
                                                  int n, int row0, int rows, double *ds, double *o_out,
                                                  double *red) {
+  if (n <= 32) return output_stats_small(type, stable, z, t, n, row0, rows, ds, o_out);
   OutStats st;
   double shift = 1.0, dv = 1.0;
   if (type == HPNN_TYPE_SNN) {

@@ -28,53 +28,73 @@ struct KP {
   int min_iter, max_iter;
   int max_ld, max_rows;  // shared-memory carve-up (doubles)
   hpnn_train_result *result;
+  long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
+  int trace_cap;
 };
 
-// Grid barrier, extended to all ranks when world > 1.  The sense is a
-// monotonically increasing epoch; the last CTA to arrive on a rank does the
-// cross-rank exchange (one release-store per peer + acquire-spin on its own
-// flag words) before releasing its grid.
+// Grid barrier, extended to all ranks when world > 1.
+//
+// Arrival is a fire-and-forget `red.release.gpu` on one of three rotating counters (no
+// round trip for a return value); everybody polls that counter with relaxed loads until it
+// reads gridDim.x and then issues one acquire fence.  CTA 0 zeroes the counter used by the
+// PREVIOUS barrier once it has passed the current one: all CTAs have left it by then, and it
+// is not needed again before barrier k+2, which cannot complete without CTA 0's own arrival
+// at k+1 (ordered after the reset).  The barrier index survives kernel launches in
+// local_sync, so the rotation simply continues with the next sample.
+//
+// With several ranks CTA 0 alone watches the counter, exchanges one flag word with every
+// peer over NVLink (fence.sys + relaxed stores, relaxed polling + fence.sys) and then
+// publishes the index in a `go` word the other CTAs poll.
+// local_sync words: [0],[32],[64] counters (own 128 B lines), [96] go, [128] saved index.
 struct Barrier {
-  unsigned *count, *release, *wepoch;
-  unsigned epoch;  // meaningful in thread 0
+  unsigned *sync;
+  unsigned k;  // barrier index, meaningful in thread 0
   __device__ __forceinline__ void init(const hpnn_dev_net &n) {
-    count = n.local_sync;
-    release = n.local_sync + 1;
-    wepoch = n.local_sync + 2;
-    epoch = (threadIdx.x == 0) ? ld_acquire_gpu(release) : 0u;
+    sync = n.local_sync;
+    k = (threadIdx.x == 0) ? ld_relaxed_gpu(sync + 128) : 0u;
   }
-  __device__ __forceinline__ void sync(const hpnn_dev_net &n) {
+  __device__ __forceinline__ void finish() {  // call once, after the last barrier
+    if (blockIdx.x == 0 && threadIdx.x == 0) sync[128] = k;
+  }
+  // `remote`: this CTA stored into a peer's arena since the last barrier (only then does
+  // it pay for a system-scope fence before arriving).
+  __device__ __forceinline__ void sync_all(const hpnn_dev_net &n, bool remote = true) {
     __syncthreads();
     if (threadIdx.x == 0) {
-      ++epoch;
-      if (n.world > 1) fence_sys();  // this CTA's peer stores are ordered before the arrive
-      const unsigned old = atom_add_acqrel_gpu(count, 1u);
-      if (old == gridDim.x - 1) {
-        *count = 0;  // nobody can arrive again before the release below
-        if (n.world > 1) {
-          const unsigned wnext = ld_acquire_gpu(wepoch) + 1u;
-          st_release_gpu(wepoch, wnext);
-          const unsigned long long we = (unsigned long long)wnext;
-          fence_sys();
-          for (int q = 0; q < n.world; ++q) {
-            if (q == n.rank) continue;
-            unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
-            st_release_sys(f, we);
-          }
-          const unsigned long long *mine =
-              reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
-          for (int q = 0; q < n.world; ++q) {
-            if (q == n.rank) continue;
-            while (ld_acquire_sys(mine + q) < we) {
-            }
+      unsigned *c = sync + 32 * (k % 3u);
+      unsigned *prev = sync + 32 * ((k + 2u) % 3u);
+      ++k;
+      if (n.world > 1 && remote) fence_sys();  // peer stores performed before the arrive
+      red_add_release_gpu(c, 1u);
+      if (n.world == 1) {
+        while (ld_relaxed_gpu(c) != gridDim.x) {
+        }
+        if (blockIdx.x == 0) *prev = 0;
+        fence_gpu();
+      } else if (blockIdx.x == 0) {
+        while (ld_relaxed_gpu(c) != gridDim.x) {
+        }
+        *prev = 0;
+        const unsigned long long we = (unsigned long long)k;
+        fence_sys();  // release: everything this rank wrote is visible before the flags
+        for (int q = 0; q < n.world; ++q) {
+          if (q == n.rank) continue;
+          unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
+          st_relaxed_sys(f, we);
+        }
+        const unsigned long long *mine = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
+        for (int q = 0; q < n.world; ++q) {
+          if (q == n.rank) continue;
+          while (ld_relaxed_sys(mine + q) < we) {
           }
         }
-        st_release_gpu(release, epoch);
+        fence_sys();  // acquire: the peers' stores into this arena are visible after it
+        st_release_gpu(sync + 96, k);
       } else {
-        while (ld_acquire_gpu(release) != epoch) {
+        while (ld_relaxed_gpu(sync + 96) != k) {
         }
+        fence_gpu();
       }
-      if (n.world > 1) fence_sys();
     }
     __syncthreads();
   }
@@ -114,6 +134,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
 
   Barrier bar;
   bar.init(n);
+  int trace_n = 0;
+  auto trace = [&](int tag) {
+    if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
+      p.trace[2 * trace_n] = tag;
+      p.trace[2 * trace_n + 1] = clock64();
+      ++trace_n;
+    }
+  };
 
   // act[i], i >= 1, is double buffered: the fused update+forward of layer 0 rewrites
   // act[1] while other CTAs may still need the old values to finish delta_0.
@@ -144,7 +172,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   }
   for (int l = 0; l < NL; ++l) {
     forward_layer(l, cur, cur, 0);
-    bar.sync(n);
+    bar.sync_all(n, (int)blockIdx.x < n.rows[l]);
   }
   const double *target = A + n.off_target;
   const int last = NL - 1;
@@ -158,6 +186,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   if (p.mode == 0) {
     for (;;) {
       ++iter;
+      trace(1);
       // ---- top-down: deltas from the old weights fused with the update
       for (int l = last; l >= 1; --l) {
         if (l != last) {
@@ -182,20 +211,27 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
         const double *h = act_of(n.rank, l, cur);
         if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, ds, h, p.lr, p.alpha, red, make_sink);
         else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, ds, h, p.lr, p.alpha, red, make_sink);
-        bar.sync(n);
+        trace(100 + l);
+        bar.sync_all(n, (int)blockIdx.x < n.ld[l] / cb);
+        trace(200 + l);
       }
       // ---- bottom-up: layer 0 update fused with its forward, then the rest
       stage_delta(n, 0, act_of(n.rank, 1, cur), ds);
       forward_layer(0, 0, cur ^ 1, upd);
-      bar.sync(n);
+      trace(300);
+      bar.sync_all(n, (int)blockIdx.x < n.rows[0]);
+      trace(400);
       for (int l = 1; l < NL; ++l) {
         forward_layer(l, cur ^ 1, cur ^ 1, 0);
-        bar.sync(n);
+        trace(300 + l);
+        bar.sync_all(n, (int)blockIdx.x < n.rows[l]);
+        trace(400 + l);
       }
       cur ^= 1;
       // ---- evaluate (every CTA, identical arithmetic => identical decision)
       st = output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, n.row0[last], n.rows[last],
                         ds, nullptr, red);
+      trace(2);
       dE = E - st.err;
       E = st.err;
       ok = (st.argmax == st.target);
@@ -208,6 +244,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     if (blockIdx.x == 0)
       output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, 0, 0, nullptr, A + n.off_out, red);
   }
+  bar.finish();
   if (blockIdx.x == 0 && threadIdx.x == 0 && p.result) {
     hpnn_train_result r;
     r.init_err = init_err;
@@ -223,6 +260,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
 
 // ------------------------------- host side ---------------------------------
 static int g_grid_override = 0;
+static long long *g_trace = nullptr;
+static int g_trace_cap = 0;
 static thread_local char g_err[512] = "";
 long long g_launches = 0;
 
@@ -246,6 +285,11 @@ long long hpnn_dev_launch_count(int reset) {
 }
 
 void hpnn_dev_set_persistent_grid(int ctas) { g_grid_override = ctas; }
+
+void hpnn_dev_set_phase_trace(long long *dev_buf, int capacity_pairs) {
+  g_trace = dev_buf;
+  g_trace_cap = dev_buf ? capacity_pairs : 0;
+}
 
 int hpnn_dev_persistent_grid(void) {
   int dev = 0, sms = 0;
@@ -304,6 +348,8 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   p.min_iter = o->min_iter >= 0 ? o->min_iter : d.min_iter;
   p.max_iter = o->max_iter >= 0 ? o->max_iter : d.max_iter;
   p.result = result_dev;
+  p.trace = g_trace;
+  p.trace_cap = g_trace_cap;
   int max_ld = 8, max_rows = 8;
   for (int l = 0; l < net->n_layers; ++l) {
     max_ld = net->ld[l] > max_ld ? net->ld[l] : max_ld;

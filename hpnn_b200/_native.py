@@ -99,6 +99,7 @@ def _declare(lib):
         "hpnn_dev_train_sample": (i, [C.POINTER(DevNet), C.POINTER(TrainOpts), i, vp, vp]),
         "hpnn_dev_persistent_grid": (i, []),
         "hpnn_dev_set_persistent_grid": (None, [i]),
+        "hpnn_dev_set_phase_trace": (None, [vp, i]),
         "hpnn_dev_forward_layer": (i, [vp, i, i, i, vp, vp, i, vp]),
         "hpnn_dev_output_stats": (i, [i, i, vp, vp, i, vp, vp, vp, vp]),
         "hpnn_dev_backward_update": (i, [vp, vp, i, i, i, vp, vp, vp, i, d, d, vp]),

@@ -90,7 +90,7 @@ class HpnnNet:
                 net.dW[l] = None
         # ---- symmetric arena + private sync words (raw cudaMalloc: IPC-exportable)
         self._arena_ptr = self.lib.hpnn_dev_alloc(n_doubles * 8)
-        self._sync_ptr = self.lib.hpnn_dev_alloc(64 * 4)
+        self._sync_ptr = self.lib.hpnn_dev_alloc(256 * 4)
         if not self._arena_ptr or not self._sync_ptr:
             raise MemoryError(N.last_error())
         self.arena = torch.as_tensor(_DevBuf(self._arena_ptr, n_doubles), device=self.device)

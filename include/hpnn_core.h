@@ -139,7 +139,7 @@ typedef struct {
   double *dW[HPNN_MAX_LAYERS];  /* momentum, same shape, or NULL            */
   int rank, world;
   double *arena[HPNN_MAX_WORLD];
-  unsigned *local_sync;         /* 64 zeroed u32 words, private to the rank  */
+  unsigned *local_sync;         /* 256 zeroed u32 words, private to the rank */
   /* arena layout (offsets in doubles), filled by hpnn_dev_arena_layout      */
   long long off_act[HPNN_MAX_LAYERS + 1]; /* act[0]=input, act[l+1]=out of l */
   long long off_part[HPNN_MAX_LAYERS];    /* per-rank partial W^T.delta      */
@@ -180,6 +180,10 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
 int hpnn_dev_persistent_grid(void);
 /* set grid (CTAs) used by K-P: 0 = one per SM (default) */
 void hpnn_dev_set_persistent_grid(int ctas);
+/* observability: when set, CTA 0 of K-P appends (tag, clock64) pairs at every phase boundary
+ * (tags: 1 iteration start, 100+l column phase l done, 200+l its barrier passed, 300+l row
+ * phase l done, 400+l its barrier passed, 2 evaluation done).  NULL switches it off. */
+void hpnn_dev_set_phase_trace(long long *dev_buf, int capacity_pairs);
 
 /* stand-alone phase kernels (K-A..K-E), one launch each, single rank or one
  * rank's slice.  Used by unit tests, by the multi-launch trainer and by the
