@@ -1,0 +1,246 @@
+// hpnn_net: a device-resident network driven from ONE host process, for C/C++ callers
+// (the libhpnn.h shim first of all).  With n_gpus > 1 it is the same row-split as the
+// PyTorch HpnnNet -- weights partitioned, one symmetric arena per GPU reachable by every
+// peer (cudaDeviceEnablePeerAccess; no IPC needed inside one process), one persistent
+// kernel per GPU per sample -- which is also how the reference drives its GPUs
+// (single process, src/libhpnn.c:201-305), minus its "everything lives on GPU 0" layout.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "hpnn_core.h"
+#include "kernel_host.hpp"
+
+namespace hpnn {
+void set_error(const char *what, cudaError_t e);
+void set_error_msg(const char *what);
+}  // namespace hpnn
+
+struct hpnn_net {
+  int type = 0, world = 1;
+  bool momentum = false;
+  std::vector<int> dims;
+  struct Rank {
+    int dev = 0;
+    hpnn_dev_net net;
+    std::vector<double *> W, dW;
+    double *arena = nullptr;
+    unsigned *sync = nullptr;
+    hpnn_train_result *res = nullptr;
+    cudaStream_t stream = nullptr;
+  };
+  std::vector<Rank> ranks;
+  double *pin = nullptr;  // pinned staging: input | target | output
+  hpnn_train_result *pin_res = nullptr;
+  size_t bytes_dev = 0;
+};
+
+#define NET_CHECK(call, what)          \
+  do {                                 \
+    cudaError_t e__ = (call);          \
+    if (e__ != cudaSuccess) {          \
+      hpnn::set_error(what, e__);      \
+      return -1;                       \
+    }                                  \
+  } while (0)
+
+extern "C" {
+
+void hpnn_net_destroy(hpnn_net *n) {
+  if (!n) return;
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    if (r.stream) cudaStreamSynchronize(r.stream);
+    for (double *p : r.W) cudaFree(p);
+    for (double *p : r.dW) cudaFree(p);
+    cudaFree(r.arena);
+    cudaFree(r.sync);
+    cudaFree(r.res);
+    if (r.stream) cudaStreamDestroy(r.stream);
+  }
+  if (n->pin) cudaFreeHost(n->pin);
+  if (n->pin_res) cudaFreeHost(n->pin_res);
+  if (!n->ranks.empty()) cudaSetDevice(n->ranks[0].dev);
+  delete n;
+}
+
+int hpnn_net_upload(hpnn_net *n, const hpnn_kernel *k) {
+  if (!n || !k || k->dims != n->dims) return -1;
+  const int NL = (int)n->dims.size() - 1;
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    for (int l = 0; l < NL; ++l) {
+      if (r.net.rows[l] == 0) continue;
+      const int M = n->dims[l];
+      const double *src = k->W[l].data() + (size_t)r.net.row0[l] * M;
+      NET_CHECK(cudaMemcpy2DAsync(r.W[l], sizeof(double) * r.net.ld[l], src, sizeof(double) * M, sizeof(double) * M,
+                                  r.net.rows[l], cudaMemcpyHostToDevice, r.stream),
+                "hpnn_net_upload");
+    }
+    NET_CHECK(cudaStreamSynchronize(r.stream), "hpnn_net_upload(sync)");
+  }
+  return 0;
+}
+
+int hpnn_net_download(hpnn_net *n, hpnn_kernel *k) {
+  if (!n || !k || k->dims != n->dims) return -1;
+  const int NL = (int)n->dims.size() - 1;
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    for (int l = 0; l < NL; ++l) {
+      if (r.net.rows[l] == 0) continue;
+      const int M = n->dims[l];
+      double *dst = k->W[l].data() + (size_t)r.net.row0[l] * M;
+      NET_CHECK(cudaMemcpy2DAsync(dst, sizeof(double) * M, r.W[l], sizeof(double) * r.net.ld[l], sizeof(double) * M,
+                                  r.net.rows[l], cudaMemcpyDeviceToHost, r.stream),
+                "hpnn_net_download");
+    }
+    NET_CHECK(cudaStreamSynchronize(r.stream), "hpnn_net_download(sync)");
+  }
+  return 0;
+}
+
+hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gpus) {
+  if (!k) return nullptr;
+  int avail = 0;
+  if (cudaGetDeviceCount(&avail) != cudaSuccess || avail < 1) {
+    cudaGetLastError();
+    hpnn::set_error_msg("hpnn_net_create: no CUDA device");
+    return nullptr;
+  }
+  if (n_gpus <= 0 || n_gpus > avail) n_gpus = avail;
+  if (n_gpus > HPNN_MAX_WORLD) n_gpus = HPNN_MAX_WORLD;
+  hpnn_net *n = new hpnn_net();
+  n->type = type;
+  n->world = n_gpus;
+  n->momentum = momentum != 0;
+  n->dims = k->dims;
+  const int NL = (int)k->dims.size() - 1;
+  n->ranks.resize(n_gpus);
+  bool ok = true;
+  // peer access all-to-all (the reference only enables it towards GPU 0, src/libhpnn.c:282-288)
+  for (int a = 0; a < n_gpus && ok; ++a)
+    for (int b = 0; b < n_gpus && ok; ++b)
+      if (a != b && hpnn_enable_peer_access(a, b) != 0) {
+        hpnn::set_error_msg("hpnn_net_create: GPUs cannot reach each other (peer access)");
+        ok = false;
+      }
+  for (int g = 0; g < n_gpus && ok; ++g) {
+    auto &r = n->ranks[g];
+    r.dev = g;
+    cudaSetDevice(g);
+    memset(&r.net, 0, sizeof(r.net));
+    r.net.n_layers = NL;
+    for (int i = 0; i <= NL; ++i) r.net.dims[i] = k->dims[i];
+    r.net.rank = g;
+    r.net.world = n_gpus;
+    const long long doubles = hpnn_dev_arena_layout(&r.net);
+    if (doubles <= 0) {
+      ok = false;
+      break;
+    }
+    r.W.assign(NL, nullptr);
+    r.dW.assign(NL, nullptr);
+    for (int l = 0; l < NL && ok; ++l) {
+      const size_t bytes = sizeof(double) * (size_t)r.net.rows[l] * r.net.ld[l];
+      r.W[l] = (double *)hpnn_dev_alloc(bytes);
+      if (n->momentum) r.dW[l] = (double *)hpnn_dev_alloc(bytes);
+      ok = r.W[l] && (!n->momentum || r.dW[l]);
+      r.net.W[l] = r.W[l];
+      r.net.dW[l] = r.dW[l];
+      n->bytes_dev += bytes * (n->momentum ? 2 : 1);
+    }
+    r.arena = (double *)hpnn_dev_alloc(sizeof(double) * (size_t)doubles);
+    r.sync = (unsigned *)hpnn_dev_alloc(256 * sizeof(unsigned));
+    r.res = (hpnn_train_result *)hpnn_dev_alloc(sizeof(hpnn_train_result));
+    n->bytes_dev += sizeof(double) * (size_t)doubles;
+    ok = ok && r.arena && r.sync && r.res && cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) == cudaSuccess;
+    r.net.local_sync = r.sync;
+  }
+  if (ok) {
+    for (auto &r : n->ranks)
+      for (int q = 0; q < n_gpus; ++q) r.net.arena[q] = n->ranks[q].arena;
+    const size_t pin_doubles = (size_t)k->dims[0] + 2 * (size_t)k->dims[NL];
+    ok = cudaMallocHost((void **)&n->pin, sizeof(double) * pin_doubles) == cudaSuccess &&
+         cudaMallocHost((void **)&n->pin_res, sizeof(hpnn_train_result)) == cudaSuccess;
+  }
+  if (ok) ok = hpnn_net_upload(n, k) == 0;
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    cudaDeviceSynchronize();
+  }
+  cudaSetDevice(0);
+  if (!ok) {
+    hpnn_net_destroy(n);
+    return nullptr;
+  }
+  return n;
+}
+
+int hpnn_net_world(const hpnn_net *n) { return n ? n->world : 0; }
+void hpnn_net_set_type(hpnn_net *n, int type) {
+  if (n) n->type = type;
+}
+long long hpnn_net_device_bytes(const hpnn_net *n) { return n ? (long long)n->bytes_dev : 0; }
+
+static int net_launch(hpnn_net *n, const hpnn_train_opts *o, int mode, const double *in, const double *target) {
+  const int NL = (int)n->dims.size() - 1;
+  const int n_in = n->dims[0], n_out = n->dims[NL];
+  memcpy(n->pin, in, sizeof(double) * n_in);
+  if (target) memcpy(n->pin + n_in, target, sizeof(double) * n_out);
+  else memset(n->pin + n_in, 0, sizeof(double) * n_out);
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    NET_CHECK(cudaMemcpyAsync(r.arena + r.net.off_act[0], n->pin, sizeof(double) * n_in, cudaMemcpyHostToDevice, r.stream),
+              "sample H2D");
+    NET_CHECK(cudaMemcpyAsync(r.arena + r.net.off_target, n->pin + n_in, sizeof(double) * n_out, cudaMemcpyHostToDevice,
+                              r.stream),
+              "target H2D");
+  }
+  // one persistent kernel per GPU; they meet in the cross-GPU barriers
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    if (hpnn_dev_train_sample(&r.net, o, mode, r.res, r.stream) != 0) return -1;
+  }
+  auto &r0 = n->ranks[0];
+  cudaSetDevice(r0.dev);
+  NET_CHECK(cudaMemcpyAsync(n->pin_res, r0.res, sizeof(hpnn_train_result), cudaMemcpyDeviceToHost, r0.stream), "result D2H");
+  NET_CHECK(cudaMemcpyAsync(n->pin + n_in + n_out, r0.arena + r0.net.off_out, sizeof(double) * n_out,
+                            cudaMemcpyDeviceToHost, r0.stream),
+            "output D2H");
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    NET_CHECK(cudaStreamSynchronize(r.stream), "hpnn_net sync");
+  }
+  cudaSetDevice(r0.dev);
+  return 0;
+}
+
+int hpnn_net_train_sample(hpnn_net *n, const hpnn_train_opts *o, const double *in, const double *target,
+                          hpnn_train_result *res, double *out) {
+  if (!n || !o || !in || !target) return -1;
+  if (o->train == HPNN_TRAIN_BPM && !n->momentum) {
+    hpnn::set_error_msg("hpnn_net_train_sample: net was created without momentum buffers");
+    return -1;
+  }
+  if (net_launch(n, o, 0, in, target) != 0) return -1;
+  if (res) *res = *n->pin_res;
+  const int NL = (int)n->dims.size() - 1;
+  if (out) memcpy(out, n->pin + n->dims[0] + n->dims[NL], sizeof(double) * n->dims[NL]);
+  return 0;
+}
+
+int hpnn_net_run(hpnn_net *n, const double *in, double *out, int stable_softmax) {
+  if (!n || !in || !out) return -1;
+  hpnn_train_opts o;
+  hpnn_train_opts_default(&o, n->type, HPNN_TRAIN_BP, 1);
+  o.stable_softmax = stable_softmax;
+  if (net_launch(n, &o, 1, in, nullptr) != 0) return -1;
+  const int NL = (int)n->dims.size() - 1;
+  memcpy(out, n->pin + n->dims[0] + n->dims[NL], sizeof(double) * n->dims[NL]);
+  return 0;
+}
+
+}  // extern "C"

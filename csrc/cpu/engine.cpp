@@ -171,6 +171,54 @@ int hpnn_cpu_forward(const hpnn_kernel *kc, int type, int stable, const double *
   return 0;
 }
 
+/* ---- single-step entry points (ann_kernel_run / ann_kernel_train* of the reference) ---- */
+double *hpnn_cpu_act(hpnn_kernel *k, int i) {
+  if (!k) return nullptr;
+  ensure_workspace(k, false);
+  return (i >= 0 && i <= k->n_layers()) ? k->act[i].data() : nullptr;
+}
+double *hpnn_cpu_momentum(hpnn_kernel *k, int l) {
+  if (!k || (int)k->dW.size() != k->n_layers() || l < 0 || l >= k->n_layers()) return nullptr;
+  return k->dW[l].data();
+}
+void hpnn_cpu_momentum_init(hpnn_kernel *k) {
+  if (k) ensure_workspace(k, true);
+}
+void hpnn_cpu_momentum_zero(hpnn_kernel *k) {
+  if (!k) return;
+  for (auto &m : k->dW) std::fill(m.begin(), m.end(), 0.0);
+}
+void hpnn_cpu_momentum_free(hpnn_kernel *k) {
+  if (k) k->dW.clear();
+}
+// forward from act[0] (already filled by the caller)
+int hpnn_cpu_forward_inplace(hpnn_kernel *k, int type, int stable) {
+  if (!k) return -1;
+  ensure_workspace(k, false);
+  forward(k, type, stable);
+  return 0;
+}
+double hpnn_cpu_error(hpnn_kernel *k, int type, const double *target) {
+  if (!k || !target) return 0.0;
+  ensure_workspace(k, false);
+  return error(k, type, target);
+}
+// one BP / BPM iteration on an already forwarded net; returns E_before - E_after.
+// Momentum persists across calls (the caller zeroes it per sample).
+double hpnn_cpu_train_iteration(hpnn_kernel *k, const hpnn_train_opts *opt, const double *target) {
+  if (!k || !opt || !target) return 0.0;
+  hpnn_train_opts d;
+  hpnn_train_opts_default(&d, opt->type, opt->train, 0);
+  const bool momentum = opt->train == HPNN_TRAIN_BPM;
+  ensure_workspace(k, momentum);
+  const double lr = opt->lr > 0 ? opt->lr : d.lr;
+  const double Ep = error(k, opt->type, target);
+  deltas(k, opt->type, target);
+  update(k, momentum, lr, opt->alpha);
+  forward(k, opt->type, opt->stable_softmax);
+  return Ep - error(k, opt->type, target);
+}
+
 int hpnn_cpu_train_sample(hpnn_kernel *k, const hpnn_train_opts *opt, const double *in, const double *t,
                           hpnn_train_result *res, double *out) {
   if (!k || !opt || !in || !t) return -1;

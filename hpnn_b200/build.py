@@ -29,6 +29,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp,-Wall,
 CORE_SOURCES = [
     "csrc/core/io.cpp",
     "csrc/cpu/engine.cpp",
+    "csrc/core/device_net.cu",
     "csrc/kernels/train_persistent.cu",
     "csrc/kernels/ops.cu",
     "csrc/kernels/gemm_umma.cu",

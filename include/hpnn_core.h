@@ -116,7 +116,18 @@ void hpnn_train_opts_default(hpnn_train_opts *o, int type, int train, int cuda_d
 void hpnn_set_omp_threads(int n);
 /* out must hold dim(n_layers) doubles */
 int hpnn_cpu_forward(const hpnn_kernel *k, int type, int stable_softmax, const double *in, double *out);
-/* one BP/BPM iteration on a forwarded net is not exposed: the per-sample loop is */
+/* single-step API (ann_kernel_run / ann_kernel_train / ann_kernel_train_momentum):
+ * act(0) is the input buffer, act(i+1) the output of layer i; momentum persists across
+ * hpnn_cpu_train_iteration calls until zeroed. */
+double *hpnn_cpu_act(hpnn_kernel *k, int i);
+double *hpnn_cpu_momentum(hpnn_kernel *k, int l);
+void hpnn_cpu_momentum_init(hpnn_kernel *k);
+void hpnn_cpu_momentum_zero(hpnn_kernel *k);
+void hpnn_cpu_momentum_free(hpnn_kernel *k);
+int hpnn_cpu_forward_inplace(hpnn_kernel *k, int type, int stable_softmax);
+double hpnn_cpu_error(hpnn_kernel *k, int type, const double *target);
+double hpnn_cpu_train_iteration(hpnn_kernel *k, const hpnn_train_opts *o, const double *target);
+/* whole per-sample convergence loop */
 int hpnn_cpu_train_sample(hpnn_kernel *k, const hpnn_train_opts *o, const double *in,
                           const double *target, hpnn_train_result *res, double *out);
 
@@ -217,6 +228,25 @@ int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void
 /* data-parallel gradient merge (extension): W += sum_ranks G_rank */
 int hpnn_dev_grad_merge(double *W, long long n, double *const *grads, int n_ranks, double scale,
                         void *stream);
+
+/* ------------------------------------------------------------------------ */
+/* hpnn_net: device-resident network driven from one host process            */
+/* ------------------------------------------------------------------------ */
+/* Owns its device memory.  n_gpus <= 0 means "all visible GPUs": the layers are then
+ * row-split over them exactly as in the multi-process PyTorch path (one persistent kernel
+ * per GPU per sample, collectives issued from inside the kernels over peer memory). */
+typedef struct hpnn_net hpnn_net;
+hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gpus);
+void hpnn_net_destroy(hpnn_net *n);
+int hpnn_net_world(const hpnn_net *n);
+void hpnn_net_set_type(hpnn_net *n, int type);
+long long hpnn_net_device_bytes(const hpnn_net *n);
+int hpnn_net_upload(hpnn_net *n, const hpnn_kernel *k);   /* host weights -> device */
+int hpnn_net_download(hpnn_net *n, hpnn_kernel *k);       /* device weights -> host */
+/* per-sample convergent training (K-P) / single forward; `out` may be NULL */
+int hpnn_net_train_sample(hpnn_net *n, const hpnn_train_opts *o, const double *in, const double *target,
+                          hpnn_train_result *res, double *out);
+int hpnn_net_run(hpnn_net *n, const double *in, double *out, int stable_softmax);
 
 /* launch counter: number of kernels this library launched since the last reset */
 long long hpnn_dev_launch_count(int reset);
