@@ -125,7 +125,7 @@ def build_tools(verbose: bool = False) -> dict:
         if src.exists():
             exe = BINDIR / name
             if not exe.exists() or exe.stat().st_mtime < src.stat().st_mtime:
-                _run([cxx, "-O2", "-std=c++17", f"-I{ROOT / 'include'}", src, "-o", exe], verbose)
+                _run([cxx, "-O2", "-std=c++17", f"-I{ROOT / 'include'}", f"-I{ROOT / 'tools'}", src, "-o", exe], verbose)
             out[name] = exe
     return out
 
