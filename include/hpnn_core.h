@@ -248,6 +248,29 @@ int hpnn_net_train_sample(hpnn_net *n, const hpnn_train_opts *o, const double *i
                           hpnn_train_result *res, double *out);
 int hpnn_net_run(hpnn_net *n, const double *in, double *out, int stable_softmax);
 
+/* Forward pass for callers that must not allocate device memory.
+ * (No counterpart in the reference: its CUDA path calls cudaMalloc per sample and per
+ * iteration, src/ann.c:2305-2310, src/cuda_ann.cu:2114-2117.)
+ * Hosts that gave the whole GPU to their own pool, or that cannot afford the device-wide
+ * synchronisation cudaMalloc/cudaFree imply, pass the padded weight matrices, the input and
+ * the output buffer (all device memory they already own); the persistent kernel's work space
+ * is a fixed array inside the library instead: HPNN_NOALLOC_SCRATCH_BYTES on every GPU that
+ * loads the library, held until the process exits.
+ *   type / stable_softmax  as in hpnn_train_opts
+ *   dims[0..n_layers]      layer widths; W[l] is [dims[l+1] x pad8(dims[l])], pad columns zero
+ *   x (dims[0] doubles)    input;  out (dims[n_layers] doubles) receives the activated /
+ *                          soft-maxed output; the call is asynchronous on `stream`
+ * Returns 0, -1 on bad arguments or a CUDA error, -2 when the network's arena layout needs
+ * more than HPNN_NOALLOC_MAX_DOUBLES doubles (nothing is launched; see hpnn_last_error()).
+ * It calls no cudaMalloc/cudaFree.  All calls on a device share the one array: calls whose
+ * GPU work overlaps race, so keep them on one stream.  The first call on each device resolves
+ * the array's address (cudaGetSymbolAddress); make that call at start-up, before any stream
+ * capture begins. */
+#define HPNN_NOALLOC_MAX_DOUBLES (128 * 1024)
+#define HPNN_NOALLOC_SCRATCH_BYTES (HPNN_NOALLOC_MAX_DOUBLES * 8 + 1024)
+int hpnn_dev_forward_noalloc(int type, int stable_softmax, int n_layers, const int *dims,
+                             const double *const *W, const double *x, double *out, void *stream);
+
 /* launch counter: number of kernels this library launched since the last reset */
 long long hpnn_dev_launch_count(int reset);
 
