@@ -257,20 +257,43 @@ def run_ours(args, cfg):
 
 # ----------------------------------------------------------------------------- reference
 def run_reference(args, cfg):
+    """Rank 0 runs the reference in a child process (the reference calls exit(-1) on any CUDA
+    or allocation error, which must not take the reporter down); other ranks idle."""
     rank, world, local = rank_world()
-    n_gpus = max(1, args.gpus)
-    out = {"impl": "reference"}
     if rank != 0:
         # the reference drives every GPU from ONE process (src/libhpnn.c:201-305): ranks > 0 idle
         _wait_for_flag(args)
         return
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE",
+                                                              "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID")}
+    env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(max(1, args.gpus)))
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--child", "--gpus", str(args.gpus),
+           "--steps", str(args.steps), "--warmup", str(args.warmup), "--config", args.config,
+           "--ref-streams", str(args.ref_streams)]
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=args.ref_timeout)
+        lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+        if r.returncode == 0 and lines:
+            print(lines[-1], flush=True)
+        else:
+            tail = (r.stderr.strip().splitlines() or r.stdout.strip().splitlines() or ["no output"])[-1]
+            print(json.dumps({"impl": "reference", "n_gpus": args.gpus, "unavailable":
+                              ("reference process exited with code %d: %s" % (r.returncode, tail))[:300]}), flush=True)
+    except subprocess.TimeoutExpired:
+        print(json.dumps({"impl": "reference", "n_gpus": args.gpus,
+                          "unavailable": "reference run exceeded %d s" % args.ref_timeout}), flush=True)
+    _set_flag(args)
+
+
+def run_reference_child(args, cfg):
+    n_gpus = max(1, args.gpus)
+    out = {"impl": "reference"}
     try:
         lib_path = os.path.join(ROOT, "baseline", "_ref", "build", "libhpnn_ref_cuda.so")
         if not os.path.exists(lib_path):
             sys.path.insert(0, os.path.join(ROOT, "baseline"))
             import build_ref
             build_ref.build(("cuda",))
-        os.environ["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(n_gpus))
         tmp = tempfile.mkdtemp(prefix="hpnn_bench_ref_")
         conf_path = make_dataset(cfg, args.warmup, args.steps, tmp)
         ref = C.CDLL(lib_path, mode=C.RTLD_GLOBAL)
@@ -344,7 +367,6 @@ def run_reference(args, cfg):
     except Exception as e:  # the contract: report and exit 0
         out = {"impl": "reference", "unavailable": ("%s: %s" % (type(e).__name__, e)).replace("\n", " ")[:300]}
     print(json.dumps(out), flush=True)
-    _set_flag(args)
 
 
 def _flag_path(args):
@@ -377,11 +399,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default=os.environ.get("HPNN_BENCH_CONFIG", "wide_ann"), choices=sorted(CONFIGS))
     ap.add_argument("--ref-streams", type=int, default=1)
+    ap.add_argument("--ref-timeout", type=int, default=3000)
+    ap.add_argument("--child", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     args.warmup = max(3, args.warmup)
     cfg = CONFIGS[args.config]
     if args.impl == "reference":
-        run_reference(args, cfg)
+        (run_reference_child if args.child else run_reference)(args, cfg)
     else:
         run_ours(args, cfg)
 

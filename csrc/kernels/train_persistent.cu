@@ -354,7 +354,7 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   for (int l = 0; l < net->n_layers; ++l) {
     max_ld = net->ld[l] > max_ld ? net->ld[l] : max_ld;
     max_rows = net->rows[l] > max_rows ? net->rows[l] : max_rows;
-    if (mode == 0 && o->train == HPNN_TRAIN_BPM && !net->dW[l]) {
+    if (mode == 0 && o->train == HPNN_TRAIN_BPM && net->rows[l] > 0 && !net->dW[l]) {
       set_error_msg("hpnn_dev_train_sample: BPM needs momentum buffers");
       return -1;
     }

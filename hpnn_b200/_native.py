@@ -116,8 +116,9 @@ def _declare(lib):
         fn.argtypes = args
     # optional entry points (present once their translation units are built)
     opt = {
-        "hpnn_dev_forward_batch_lowp": (i, [vp, i, i, i, vp, i, i, vp, i, i, i, vp]),
-        "hpnn_umma_selftest": (i, [vp, vp, vp, i, i, i, vp]),
+        "hpnn_dev_cast_bf16": (i, [vp, i, i, i, vp, i, vp]),
+        "hpnn_dev_gemm_bf16": (i, [vp, i, i, i, vp, i, i, vp, i, i, vp]),
+        "hpnn_dev_forward_noalloc": (i, [i, i, i, C.POINTER(i), C.POINTER(vp), vp, vp, vp]),
     }
     for name, (res, args) in opt.items():
         if hasattr(lib, name):

@@ -115,13 +115,32 @@ def forward_batch(Wp: torch.Tensor, cols: int, X: torch.Tensor, act_kind: int = 
                                                Y.data_ptr(), Y.stride(0), act_kind, _s()),
                 "hpnn_dev_forward_batch_f64")
     elif precision == "bf16":
-        if not hasattr(lib, "hpnn_dev_forward_batch_lowp"):
-            raise RuntimeError("this build has no tcgen05 low-precision path")
-        N.check(lib.hpnn_dev_forward_batch_lowp(Wp.data_ptr(), ld, rows, cols, X.data_ptr(), X.stride(0), B,
-                                                Y.data_ptr(), Y.stride(0), act_kind, 0, _s()),
-                "hpnn_dev_forward_batch_lowp")
+        Wb = cast_bf16(Wp, cols)
+        Xb = cast_bf16(X, cols)
+        gemm_bf16(Wb, Xb, cols, Y, act_kind)
     else:
         raise ValueError(f"unknown precision {precision!r}")
+    return Y
+
+
+def cast_bf16(A: torch.Tensor, cols: int) -> torch.Tensor:
+    """fp64 ``[R, >=cols]`` -> bf16 ``[R, pad8(cols)]`` (zero padded) with the native cast kernel."""
+    lib = N.load()
+    rows = A.shape[0]
+    ld = (cols + 7) & ~7
+    out = torch.empty((rows, ld), dtype=torch.bfloat16, device=A.device)
+    N.check(lib.hpnn_dev_cast_bf16(A.data_ptr(), A.stride(0), rows, cols, out.data_ptr(), ld, _s()), "hpnn_dev_cast_bf16")
+    return out
+
+
+def gemm_bf16(Wb: torch.Tensor, Xb: torch.Tensor, cols: int, Y: Optional[torch.Tensor] = None, act_kind: int = 1) -> torch.Tensor:
+    """K-T: ``Y = f(Xb Wb^T)`` on tcgen05 tensor cores (bf16 in, fp32 accumulate, fp64 out)."""
+    lib = N.load()
+    rows, B = Wb.shape[0], Xb.shape[0]
+    if Y is None:
+        Y = torch.empty((B, rows), dtype=torch.float64, device=Wb.device)
+    N.check(lib.hpnn_dev_gemm_bf16(Wb.data_ptr(), Wb.stride(0), rows, cols, Xb.data_ptr(), Xb.stride(0), B, Y.data_ptr(),
+                                   Y.stride(0), act_kind, _s()), "hpnn_dev_gemm_bf16")
     return Y
 
 

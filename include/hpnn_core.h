@@ -222,6 +222,13 @@ int hpnn_dev_update_forward(double *W, double *dW, int ld, int rows, int cols, c
 /* batched inference (extension): Y[B x N] = f(X[B x M] . W^T), fp64 */
 int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, const double *X, int ldx,
                                int batch, double *Y, int ldy, int act_kind, void *stream);
+/* opt-in reduced precision (K-T): bf16 operands, fp32 accumulation on the tcgen05 tensor cores
+ * (TMA -> shared memory -> tcgen05.mma -> TMEM -> epilogue), FP64 result.  Never used for parity.
+ * hpnn_dev_cast_bf16 converts an fp64 matrix (zero-filling up to ld_dst); Wb/Xb must be 16-byte
+ * aligned with leading dimensions that are multiples of 8. */
+int hpnn_dev_cast_bf16(const double *src, int ld_src, int rows, int cols, void *dst_bf16, int ld_dst, void *stream);
+int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y,
+                       int ldy, int act_kind, void *stream);
 /* row-wise softmax exp(z-1)/(TINY+sum) on a [batch x n] matrix (in place) */
 int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void *stream);
 
