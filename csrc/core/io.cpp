@@ -510,6 +510,29 @@ int hpnn_sample_read(const char *path, double **in, int *n_in, double **out, int
   return rc;
 }
 
+// Parse many sample files in parallel (OpenMP) straight into two dense row-major matrices:
+// the data-loader behind SampleSet / the pipelined training pass.  ok[i] = 1 when file i was
+// read and has exactly n_in / n_out values; returns the number of good files.
+int hpnn_sample_read_many(const char *const *paths, int n, int n_in, int n_out, double *X, double *T, unsigned char *ok) {
+  int good = 0;
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : good)
+  for (int i = 0; i < n; ++i) {
+    double *in = nullptr, *out = nullptr;
+    int ni = 0, no = 0;
+    const int rc = hpnn_sample_read(paths[i], &in, &ni, &out, &no);
+    const bool fine = rc == 0 && ni == n_in && no == n_out;
+    if (fine) {
+      memcpy(X + (size_t)i * n_in, in, sizeof(double) * n_in);
+      memcpy(T + (size_t)i * n_out, out, sizeof(double) * n_out);
+      ++good;
+    }
+    if (ok) ok[i] = fine ? 1 : 0;
+    free(in);
+    free(out);
+  }
+  return good;
+}
+
 int hpnn_sample_write(const char *path, const double *in, int n_in, const double *out, int n_out,
                       const char *comment) {
   FILE *fp = path ? fopen(path, "w") : nullptr;

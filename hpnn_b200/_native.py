@@ -73,6 +73,7 @@ def _declare(lib):
         "hpnn_conf_free": (None, [C.POINTER(Conf)]),
         "hpnn_sample_read": (i, [C.c_char_p, C.POINTER(dp), C.POINTER(i), C.POINTER(dp), C.POINTER(i)]),
         "hpnn_sample_write": (i, [C.c_char_p, dp, i, dp, i, C.c_char_p]),
+        "hpnn_sample_read_many": (i, [C.POINTER(C.c_char_p), i, i, i, vp, vp, vp]),
         "hpnn_dir_list": (i, [C.c_char_p, C.POINTER(C.POINTER(C.c_char_p)), C.POINTER(i)]),
         "hpnn_dir_list_free": (None, [C.POINTER(C.c_char_p), i]),
         "hpnn_shuffle_order": (None, [C.c_uint, i, C.POINTER(i)]),

@@ -83,21 +83,34 @@ class SampleSet:
     def __init__(self, paths: Sequence[str]):
         import torch
 
-        xs, ts, keep = [], [], []
-        for p in paths:
+        paths = list(paths)
+        self.paths: List[str] = []
+        self.inputs = torch.empty(0, 0, dtype=torch.float64)
+        self.targets = torch.empty(0, 0, dtype=torch.float64)
+        first = None
+        for p in paths:  # the first readable file fixes the shape
             try:
-                x, t = read_sample(p)
+                first = read_sample(p)
+                break
             except IOError:
-                continue  # the reference skips unreadable samples silently
-            xs.append(x)
-            ts.append(t)
-            keep.append(p)
-        self.paths = keep
-        self.inputs = torch.from_numpy(np.stack(xs)) if xs else torch.empty(0, 0, dtype=torch.float64)
-        self.targets = torch.from_numpy(np.stack(ts)) if ts else torch.empty(0, 0, dtype=torch.float64)
-        if torch.cuda.is_available() and xs:
-            self.inputs = self.inputs.pin_memory()
-            self.targets = self.targets.pin_memory()
+                continue
+        if first is None:
+            return
+        n_in, n_out = first[0].size, first[1].size
+        pin = torch.cuda.is_available()
+        X = torch.zeros((len(paths), n_in), dtype=torch.float64, pin_memory=pin)
+        T = torch.zeros((len(paths), n_out), dtype=torch.float64, pin_memory=pin)
+        ok = np.zeros(len(paths), dtype=np.uint8)
+        arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
+        N.load().hpnn_sample_read_many(arr, len(paths), n_in, n_out, X.data_ptr(), T.data_ptr(), ok.ctypes.data)
+        if ok.all():
+            self.paths, self.inputs, self.targets = paths, X, T
+        else:  # the reference skips unreadable samples silently
+            keep = torch.from_numpy(ok.astype(bool))
+            self.paths = [p for p, k in zip(paths, ok) if k]
+            self.inputs, self.targets = X[keep], T[keep]
+            if pin:
+                self.inputs, self.targets = self.inputs.pin_memory(), self.targets.pin_memory()
 
     def __len__(self):
         return len(self.paths)

@@ -81,6 +81,9 @@ int hpnn_conf_dump(const hpnn_conf *c, int n_dims, const int *dims, FILE *fp);
 int hpnn_sample_read(const char *path, double **in, int *n_in, double **out, int *n_out);
 int hpnn_sample_write(const char *path, const double *in, int n_in, const double *out, int n_out,
                       const char *comment);
+/* parallel loader: file i -> row i of X [n x n_in] and T [n x n_out]; ok[i]=1 if it matched */
+int hpnn_sample_read_many(const char *const *paths, int n, int n_in, int n_out, double *X, double *T,
+                          unsigned char *ok);
 /* readdir() order, dot-files skipped; names is a malloc'd array of malloc'd strings */
 int hpnn_dir_list(const char *dir, char ***names, int *n);
 void hpnn_dir_list_free(char **names, int n);
