@@ -202,6 +202,10 @@ def make_engine(backend: str, kernel: Kernel, nn_type: int, train: int, **kw):
         return CudaEngine(kernel, nn_type, train, **kw)
     if backend == "cpu":
         return CpuEngine(kernel, nn_type, train, **kw)
+    if backend.startswith("logical"):  # "logical" or "logical:P": multi-launch path, P logical ranks
+        from .parallel.logical import LogicalRanksEngine
+        world = int(backend.split(":")[1]) if ":" in backend else kw.pop("world", 1)
+        return LogicalRanksEngine(kernel, nn_type, train, world=world, **kw)
     if backend.startswith("torch"):
         dev = kw.pop("device", None) or ("cuda" if backend == "torch-cuda" else "cpu")
         return TorchEngine(kernel, nn_type, train, device=dev, **kw)

@@ -74,6 +74,33 @@ def main():
             if not (e_f < 1e-6 and e_c < 1e-6 and e_o < 1e-6):
                 fails += 1
         fused.close()
+    # ---- data-parallel gradient merge (extension): fused peer-load merge == NCCL all_reduce == serial sum
+    from hpnn_b200.parallel.dp import DataParallelTrainer
+    from hpnn_b200.ops import reference as R
+
+    k, _ = hp.generate_kernel(5, 50, [30, 20], 6)
+    X, T = problem(N.TYPE_ANN, 50, 6, world * 3, 3)
+    a = DataParallelTrainer(k, N.TYPE_ANN, lr=0.01, group=group, merge="fused")
+    b = DataParallelTrainer(k, N.TYPE_ANN, lr=0.01, group=group, merge="nccl")
+    Wser = [torch.from_numpy(w.copy()).cuda() for w in k.weights]
+    for s in range(3):
+        a.step(X[s * world + rank], T[s * world + rank])
+        b.step(X[s * world + rank], T[s * world + rank])
+        upd = [torch.zeros_like(w) for w in Wser]
+        for r in range(world):  # serial reference: sum of the per-sample updates from the same weights
+            xs = torch.from_numpy(X[s * world + r]).cuda(); ts = torch.from_numpy(T[s * world + r]).cuda()
+            acts = R.forward(Wser, xs, N.TYPE_ANN); d = R.deltas(Wser, acts, ts, N.TYPE_ANN)
+            for l in range(len(Wser)):
+                upd[l] += torch.outer(0.01 * d[l], acts[l])
+        for l in range(len(Wser)):
+            Wser[l] += upd[l]
+    e_ab = max(float((x - y).abs().max()) for x, y in zip(a.W, b.W))
+    e_as = max(float((x - y).abs().max()) for x, y in zip(a.W, Wser))
+    if rank == 0:
+        print(f"case dp-merge world={world}: max|fused-nccl|={e_ab:.2e} max|fused-serial|={e_as:.2e}", flush=True)
+    if not (e_ab < 1e-13 and e_as < 1e-13):
+        fails += 1
+    a.close(); b.close()
     flag = torch.tensor([fails], device="cuda")
     dist.all_reduce(flag)
     if rank == 0:

@@ -83,3 +83,23 @@ def test_native_library_is_the_one_in_tree():
     gpu.train(np.zeros(20), np.array([1.0, -1, -1, -1]))
     assert ops.launch_count() == before + 1  # one cooperative launch per sample
     gpu.close()
+
+
+@pytest.mark.parametrize("world", [1, 3, 8])
+@pytest.mark.parametrize("nn_type,train", [(N.TYPE_ANN, N.TRAIN_BP), (N.TYPE_SNN, N.TRAIN_BPM)])
+def test_multi_launch_path_with_logical_ranks(world, nn_type, train):
+    """K-A..K-E driven from the host over P logical ranks on one GPU (the successor of the
+    reference's DEBUG fake-multi-GPU build) equals the single-rank CPU engine."""
+    from hpnn_b200.trainer import make_engine
+
+    k, _ = hp.generate_kernel(21, 40, [17, 13], 6)
+    X, T = make_problem(nn_type, 40, (17, 13), 6, n_samples=2, seed=4)
+    kw = dict(max_iter=60, min_iter=70, delta=1e-300)
+    eng = make_engine(f"logical:{world}", k, nn_type, train, **kw)
+    cpu = CpuEngine(k, nn_type, train, cuda_defaults=True, **kw)
+    for x, t in zip(X, T):
+        a, b = eng.train(x, t), cpu.train(x, t)
+        assert a.n_iter == b.n_iter == 61 and abs(a.last_err - b.last_err) < 1e-12
+    for wa, wb in zip(eng.kernel().weights, cpu.kernel().weights):
+        np.testing.assert_allclose(wa, wb, atol=1e-12)
+    np.testing.assert_allclose(eng.run(X[0]), cpu.run(X[0]), atol=1e-12)
