@@ -247,9 +247,39 @@ def classify(out: np.ndarray, target: np.ndarray, nn_type: int):
 
 
 # --------------------------------------------------------------------------- drivers
-def train_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, pipeline: bool = True, **engine_kw) -> bool:
+class _Nvtx:
+    """NVTX range when CUDA is up (shows the per-sample / per-pass structure in Nsight)."""
+
+    def __init__(self, name: str):
+        self.name, self.on = name, torch.cuda.is_available()
+
+    def __enter__(self):
+        if self.on:
+            torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *a):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+
+
+def _write_metrics(path: Optional[str], record: dict) -> None:
+    if path:
+        import json
+
+        with open(path, "a") as f:
+            f.write(json.dumps(record) + "\n")
+
+
+def train_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, pipeline: bool = True,
+                 checkpoint_every: int = 0, checkpoint_path: str = "kernel.ckpt", metrics_path: Optional[str] = None,
+                 **engine_kw) -> bool:
     """``nn_train_kernel`` (src/libhpnn.c:1149-1305): one pass over ``conf.samples`` in the
-    reference's pseudo-random order; ``conf.kernel`` is replaced by the trained kernel."""
+    reference's pseudo-random order; ``conf.kernel`` is replaced by the trained kernel.
+
+    Beyond the reference (which loses the whole pass on a crash): ``checkpoint_every=n``
+    dumps the kernel (text + exact binary sidecar) every n samples, ``metrics_path`` appends one
+    JSON record per sample (``HPNN_METRICS`` env var as default)."""
+    metrics_path = metrics_path or os.environ.get("HPNN_METRICS")
     out = stream or sys.stdout
     if conf.kernel is None or conf.samples is None or conf.type == N.TYPE_UKN:
         return False
@@ -269,7 +299,7 @@ def train_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, pipel
     backend = backend or default_backend()
     eng = make_engine(backend, conf.kernel, conf.type, conf.train, **engine_kw)
     try:
-        if backend == "cuda" and pipeline:
+        if backend == "cuda" and pipeline and not checkpoint_every:
             sset = SampleSet(files)
             results = eng.train_many(sset.inputs, sset.targets) if len(sset) else []
             by_path = dict(zip(sset.paths, results))
@@ -277,20 +307,32 @@ def train_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, pipel
                 log.nn_out(_line_training_file(f), out)
                 if f in by_path:
                     log.nn_cout(format_train_result(by_path[f], conf.type, conf.train), out)
+                    _write_metrics(metrics_path, {"file": os.path.basename(f), **by_path[f].__dict__})
                     if by_path[f].final_de > 0.1:
                         log.nn_dbg("bad optimization!\n", out)
         else:
+            n_done = 0
             for f in files:
                 log.nn_out(_line_training_file(f), out)
                 try:
                     x, t = read_sample(f)
                 except IOError:
                     continue
-                r = eng.train(x, t)
+                with _Nvtx("train_sample " + os.path.basename(f)):
+                    r = eng.train(x, t)
                 log.nn_cout(format_train_result(r, conf.type, conf.train), out)
+                _write_metrics(metrics_path, {"file": os.path.basename(f), **r.__dict__})
                 if r.final_de > 0.1:
                     log.nn_dbg("bad optimization!\n", out)
                 out.flush()
+                n_done += 1
+                if checkpoint_every and n_done % checkpoint_every == 0:
+                    from .kernel_io import dump_kernel, dump_kernel_binary
+
+                    ck = eng.kernel()
+                    if int(os.environ.get("RANK", "0")) == 0:
+                        dump_kernel(ck, checkpoint_path)
+                        dump_kernel_binary(ck, checkpoint_path + ".bin")
         conf.kernel = eng.kernel()
     finally:
         eng.close()

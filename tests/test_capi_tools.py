@@ -246,3 +246,22 @@ def test_gen_ann(tmp_path):
     k = hp.load_kernel(str(p))
     assert k.dims == [6, 5, 4, 3] and k.name == "auto"
     assert np.abs(k.weights[0]).max() <= 1 / np.sqrt(5) + 1e-5  # scaled by the neuron count (reference quirk)
+
+
+def test_checkpoint_and_metrics(tmp_path):
+    import json
+
+    from hpnn_b200.kernel_io import load_kernel_binary
+
+    d = _golden_dir(tmp_path)
+    conf = hp.load_conf(str(d / "nn.conf"))
+    conf.samples = str(d / "samples")
+    ck = str(d / "kernel.ckpt")
+    assert hp.train_kernel(conf, backend="cpu", checkpoint_every=2, checkpoint_path=ck, metrics_path=str(d / "m.jsonl"),
+                           max_iter=200)
+    recs = [json.loads(l) for l in open(d / "m.jsonl")]
+    assert len(recs) == 6 and all(r["n_iter"] == 201 for r in recs)
+    k_txt, k_bin = hp.load_kernel(ck), load_kernel_binary(ck + ".bin")
+    assert k_txt.dims == k_bin.dims == [8, 5, 4, 3]
+    for a, b in zip(k_bin.weights, conf.kernel.weights):  # last checkpoint == end of pass (6 % 2 == 0)
+        assert (a == b).all()
