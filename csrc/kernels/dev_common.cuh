@@ -369,11 +369,18 @@ struct OutStats {
 // Small output layers (n <= 32, the MNIST shape has 10): every warp evaluates the whole
 // vector redundantly with shuffles only, so the per-iteration evaluation costs one L2 round
 // trip and a single __syncthreads instead of ~10 block-wide reductions.
+// ZS: z lives in shared memory (already gathered by the caller) instead of global memory
+template <bool ZS>
+__device__ __forceinline__ double ld_z(const double *p) {
+  return ZS ? *p : ldg_cg(p);
+}
+
+template <bool ZS>
 __device__ __forceinline__ OutStats output_stats_small(int type, int stable, const double *z, const double *t,
                                                        int n, int row0, int rows, double *ds, double *o_out) {
   const int lane = threadIdx.x & 31;
   const bool in = lane < n;
-  double o = in ? ldg_cg(z + lane) : 0.0;
+  double o = in ? ld_z<ZS>(z + lane) : 0.0;
   const double tj = in ? ldg_cg(t + lane) : 0.0;
   if (type == HPNN_TYPE_SNN) {
     double shift = 1.0;
@@ -384,10 +391,10 @@ __device__ __forceinline__ OutStats output_stats_small(int type, int stable, con
       shift = m;
     }
     const double e = in ? exp(o - shift) : 0.0;
-    double s = e;
-    // fixed order: sequential sum over lanes (matches the CPU engine's loop order)
-    double dv = HPNN_TINY;  // same order as the CPU engine: TINY + e_0 + e_1 + ...
-    for (int k = 0; k < n; ++k) dv += __shfl_sync(0xffffffffu, s, k);
+    double dv = e;  // butterfly sum: every lane ends with the same value
+#pragma unroll
+    for (int k = 16; k; k >>= 1) dv += __shfl_xor_sync(0xffffffffu, dv, k);
+    dv += HPNN_TINY;
     o = e / dv;
   }
   double term, d;
@@ -398,8 +405,9 @@ __device__ __forceinline__ OutStats output_stats_small(int type, int stable, con
     term = in ? (tj - o) * (tj - o) : 0.0;
     d = (tj - o) * dact_f(o);
   }
-  double e = 0.0;
-  for (int k = 0; k < n; ++k) e += __shfl_sync(0xffffffffu, term, k);
+  double e = term;
+#pragma unroll
+  for (int k = 16; k; k >>= 1) e += __shfl_xor_sync(0xffffffffu, e, k);
   double bv = (in && o == o) ? o : -INFINITY;
   int bi = in ? lane : 0x7fffffff;
   int trg = (in && tj == 1.0) ? lane : -1;
@@ -425,26 +433,27 @@ __device__ __forceinline__ OutStats output_stats_small(int type, int stable, con
   return st;
 }
 
+template <bool ZS = false>
 __device__ __forceinline__ OutStats output_stats(int type, int stable, const double *z, const double *t,
                                                  int n, int row0, int rows, double *ds, double *o_out,
                                                  double *red) {
-  if (n <= 32) return output_stats_small(type, stable, z, t, n, row0, rows, ds, o_out);
+  if (n <= 32) return output_stats_small<ZS>(type, stable, z, t, n, row0, rows, ds, o_out);
   OutStats st;
   double shift = 1.0, dv = 1.0;
   if (type == HPNN_TYPE_SNN) {
     if (stable) {
       double m = -INFINITY;
-      for (int j = threadIdx.x; j < n; j += blockDim.x) m = fmax(m, ldg_cg(z + j));
+      for (int j = threadIdx.x; j < n; j += blockDim.x) m = fmax(m, ld_z<ZS>(z + j));
       shift = block_max(m, red);
     }
     double s = 0.0;
-    for (int j = threadIdx.x; j < n; j += blockDim.x) s += exp(ldg_cg(z + j) - shift);
+    for (int j = threadIdx.x; j < n; j += blockDim.x) s += exp(ld_z<ZS>(z + j) - shift);
     dv = block_sum(s, red) + HPNN_TINY;
   }
   double e = 0.0, best = -INFINITY;
   int besti = 0x7fffffff, trg = -1;
   for (int j = threadIdx.x; j < n; j += blockDim.x) {
-    double o = ldg_cg(z + j);
+    double o = ld_z<ZS>(z + j);
     if (type == HPNN_TYPE_SNN) o = exp(o - shift) / dv;
     const double tj = ldg_cg(t + j);
     double d;

@@ -91,7 +91,14 @@ extern "C" int hpnn_dev_forward_noalloc(int type, int stable_softmax, int n_laye
   }
   net.rank = 0;
   net.world = 1;
-  const long long need = hpnn_dev_arena_layout(&net);
+  long long need = hpnn_dev_arena_layout(&net);
+  if (need > 0 && net.cta_slots > 0) {
+    // the optional per-CTA slots of the shared-memory-resident trainer are the last region of
+    // the layout; a forward pass does not need them, so they do not count against the limit
+    need = net.off_cta_part[1];
+    net.cta_slots = 0;
+    net.arena_doubles = need;
+  }
   if (need <= 0 || need > (long long)HPNN_NOALLOC_MAX_DOUBLES) {
     char msg[256];
     snprintf(msg, sizeof(msg),

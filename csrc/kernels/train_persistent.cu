@@ -17,95 +17,9 @@
 // reference's ~3*NL+4 device-wide syncs and 5 (9) passes.
 #include <stdio.h>
 
-#include "dev_common.cuh"
+#include "kp_common.cuh"
 
 namespace hpnn {
-
-struct KP {
-  hpnn_dev_net net;
-  int type, train, mode, stable;
-  double lr, alpha, thr;
-  int min_iter, max_iter;
-  int max_ld, max_rows;  // shared-memory carve-up (doubles)
-  hpnn_train_result *result;
-  long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
-  int trace_cap;
-};
-
-// Grid barrier, extended to all ranks when world > 1.
-//
-// Arrival is a fire-and-forget `red.release.gpu` on one of three rotating counters (no
-// round trip for a return value); everybody polls that counter with relaxed loads until it
-// reads gridDim.x and then issues one acquire fence.  CTA 0 zeroes the counter used by the
-// PREVIOUS barrier once it has passed the current one: all CTAs have left it by then, and it
-// is not needed again before barrier k+2, which cannot complete without CTA 0's own arrival
-// at k+1 (ordered after the reset).  The barrier index survives kernel launches in
-// local_sync, so the rotation simply continues with the next sample.
-//
-// With several ranks CTA 0 alone watches the counter, exchanges one flag word with every
-// peer over NVLink (fence.sys + relaxed stores, relaxed polling + fence.sys) and then
-// publishes the index in a `go` word the other CTAs poll.
-// local_sync words: [0],[32],[64] counters (own 128 B lines), [96] go, [128] saved index.
-struct Barrier {
-  unsigned *sync;
-  unsigned k;  // barrier index, meaningful in thread 0
-  __device__ __forceinline__ void init(const hpnn_dev_net &n) {
-    sync = n.local_sync;
-    k = (threadIdx.x == 0) ? ld_relaxed_gpu(sync + 128) : 0u;
-  }
-  __device__ __forceinline__ void finish() {  // call once, after the last barrier
-    if (blockIdx.x == 0 && threadIdx.x == 0) sync[128] = k;
-  }
-  // `remote`: this CTA stored into a peer's arena since the last barrier (only then does
-  // it pay for a system-scope fence before arriving).
-  __device__ __forceinline__ void sync_all(const hpnn_dev_net &n, bool remote = true) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      unsigned *c = sync + 32 * (k % 3u);
-      unsigned *prev = sync + 32 * ((k + 2u) % 3u);
-      ++k;
-      if (n.world > 1 && remote) fence_sys();  // peer stores performed before the arrive
-      red_add_release_gpu(c, 1u);
-      if (n.world == 1) {
-        while (ld_relaxed_gpu(c) != gridDim.x) {
-        }
-        if (blockIdx.x == 0) *prev = 0;
-        fence_gpu();
-      } else if (blockIdx.x == 0) {
-        while (ld_relaxed_gpu(c) != gridDim.x) {
-        }
-        *prev = 0;
-        const unsigned long long we = (unsigned long long)k;
-        fence_sys();  // release: everything this rank wrote is visible before the flags
-        for (int q = 0; q < n.world; ++q) {
-          if (q == n.rank) continue;
-          unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
-          st_relaxed_sys(f, we);
-        }
-        const unsigned long long *mine = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
-        for (int q = 0; q < n.world; ++q) {
-          if (q == n.rank) continue;
-          while (ld_relaxed_sys(mine + q) < we) {
-          }
-        }
-        fence_sys();  // acquire: the peers' stores into this arena are visible after it
-        st_release_gpu(sync + 96, k);
-      } else {
-        while (ld_relaxed_gpu(sync + 96) != k) {
-        }
-        fence_gpu();
-      }
-    }
-    __syncthreads();
-  }
-};
-
-__device__ __forceinline__ int pad8(int v) { return (v + 7) & ~7; }
-// inverse of row0(g) = floor(g*n/world)
-__device__ __forceinline__ int owner_of_row(int row, int n, int world) {
-  return (int)(((long long)(row + 1) * world - 1) / n);
-}
-__device__ __forceinline__ int row0_of(int g, int n, int world) { return (int)((long long)g * n / world); }
 
 // delta_l[r] = dact(h_l[r]) * sum_g part_l[g][r] for the owned rows, into shared memory
 __device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, const double *act_next, double *ds) {
@@ -258,6 +172,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   }
 }
 
+// defined in train_resident.cu: 0 = launched, < 0 = error, 1 = not eligible (use the streaming kernel)
+int launch_resident_if_eligible(const KP &p, int grid, void *stream);
+
 // ------------------------------- host side ---------------------------------
 static int g_grid_override = 0;
 static long long *g_trace = nullptr;
@@ -327,6 +244,21 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
   off += pad(net->dims[NL]);
   net->off_flags = off;
   off += 2 * HPNN_MAX_WORLD;
+  // per-CTA partial slots of the resident trainer (single rank, modest layers only)
+  net->cta_slots = 0;
+  for (int l = 0; l < NL; ++l) net->off_cta_part[l] = 0;
+  if (W == 1) {
+    long long cols = 0;
+    for (int l = 1; l < NL; ++l) cols += net->ld[l];
+    const int slots = 160;  // >= SM count of every Blackwell / Hopper part
+    if (cols * slots * 16 <= (32LL << 20)) {
+      net->cta_slots = slots;
+      for (int l = 1; l < NL; ++l) {
+        net->off_cta_part[l] = off;
+        off += 2LL * slots * net->ld[l];  // {value, tag} pairs
+      }
+    }
+  }
   net->arena_doubles = off;
   return off;
 }
@@ -361,6 +293,15 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   }
   p.max_ld = max_ld;
   p.max_rows = (max_rows + 7) & ~7;
+  const int grid = hpnn_dev_persistent_grid();
+  {
+    // small nets: keep every weight (and momentum) row in shared memory for the whole sample
+    const int rc = launch_resident_if_eligible(p, grid, stream);
+    if (rc <= 0) {
+      if (rc == 0) ++g_launches;
+      return rc;
+    }
+  }
   const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles);
   if (smem > 227 * 1024) {
     set_error_msg("hpnn_dev_train_sample: layer too wide for the persistent kernel (use the multi-launch path)");
@@ -371,7 +312,6 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
     set_error("cudaFuncSetAttribute(k_train_sample)", e);
     return -1;
   }
-  const int grid = hpnn_dev_persistent_grid();
   void *args[] = {(void *)&p};
   e = cudaLaunchCooperativeKernel((const void *)k_train_sample, dim3(grid), dim3(kThreads), args, smem,
                                   (cudaStream_t)stream);

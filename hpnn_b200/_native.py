@@ -42,7 +42,8 @@ class DevNet(C.Structure):
                 ("local_sync", C.c_void_p),
                 ("off_act", C.c_longlong * (MAX_LAYERS + 1)), ("off_part", C.c_longlong * MAX_LAYERS),
                 ("off_target", C.c_longlong), ("off_out", C.c_longlong), ("off_flags", C.c_longlong),
-                ("arena_doubles", C.c_longlong), ("part_stride", C.c_int * MAX_LAYERS)]
+                ("arena_doubles", C.c_longlong), ("part_stride", C.c_int * MAX_LAYERS),
+                ("off_cta_part", C.c_longlong * MAX_LAYERS), ("cta_slots", C.c_int)]
 
 
 _lib = None

@@ -31,12 +31,13 @@ CORE_SOURCES = [
     "csrc/cpu/engine.cpp",
     "csrc/core/device_net.cu",
     "csrc/kernels/train_persistent.cu",
+    "csrc/kernels/train_resident.cu",
     "csrc/kernels/ops.cu",
     "csrc/kernels/gemm_umma.cu",
     "csrc/kernels/noalloc.cu",
 ]
 SHIM_SOURCES = ["csrc/capi/libhpnn.cpp"]
-HEADERS = ["include/hpnn_core.h", "csrc/core/kernel_host.hpp", "csrc/kernels/dev_common.cuh",
+HEADERS = ["include/hpnn_core.h", "csrc/core/kernel_host.hpp", "csrc/kernels/dev_common.cuh", "csrc/kernels/kp_common.cuh",
            "include/libhpnn.h", "include/libhpnn/common.h", "include/libhpnn/ann.h", "include/libhpnn/snn.h"]
 
 

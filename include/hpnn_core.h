@@ -162,6 +162,10 @@ typedef struct {
   long long off_flags;                    /* cross-rank barrier flags        */
   long long arena_doubles;                /* total size                      */
   int part_stride[HPNN_MAX_LAYERS];       /* max owned rows of layer l       */
+  /* single-rank only: per-CTA partial W^T.delta slots of the shared-memory-resident trainer,
+   * cta_slots x ld[l] {value, tag} pairs for layer l >= 1 (0 slots = variant not available) */
+  long long off_cta_part[HPNN_MAX_LAYERS];
+  int cta_slots;
 } hpnn_dev_net;
 
 /* fills ld/row0/rows/offsets from dims/rank/world; returns arena size in doubles */
