@@ -225,22 +225,55 @@ __device__ __forceinline__ double warp_row(double *wrow, double *mrow, const dou
   return a;
 }
 
-// all owned rows of one layer, spread over the whole grid; result r goes to
-// dst.p[q][r] for every q (caller pre-offsets the pointers to the owned slice)
+// Segments per row chosen so that (rows of this CTA) x segments divides evenly over the 16
+// warps: 8192 rows on 148 CTAs are 55.4 rows per CTA = 3.5 rows per warp, i.e. every fourth
+// round is half empty; two half rows per row make it 6.9 -> 7 even rounds.
+__host__ __device__ inline int pick_row_segments(int rows, int ld, int grid) {
+  const int rpc = (rows + grid - 1) / grid;
+  int best = 1;
+  long long best_cost = -1;
+  for (int sg = 1; sg <= 8; sg *= 2) {
+    if (sg > 1 && ld / sg < 256) break;  // keep segments >= 2 KB
+    const long long cost = (long long)((rpc * sg + kWarps - 1) / kWarps) * ((ld + sg - 1) / sg);
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best = sg;
+    }
+  }
+  return best;
+}
+__host__ __device__ inline int row_part_doubles(int rows, int grid) { return ((rows + grid - 1) / grid) * 8; }
+
+// all owned rows of one layer, spread over the whole grid: row r belongs to CTA r % grid, its
+// `segs` segments are dealt round-robin to the warps; partial dot products meet in `rowpart`
+// (shared, row_part_doubles() doubles) and are added in segment order.  Result r goes to
+// dst.p[q][r] for every q (caller pre-offsets the pointers to the owned slice).
 template <int UPD>
 __device__ __forceinline__ void phase_rows(double *W, double *dW, int ld, int rows, const double *xs,
                                            const double *ds, double lr, double alpha, int act_kind,
-                                           const Dst &dst) {
+                                           const Dst &dst, int segs, double *rowpart) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int r = blockIdx.x + gridDim.x * warp; r < rows; r += gridDim.x * kWarps) {
-    double *wrow = W + (size_t)r * ld;
-    double *mrow = (UPD == 2) ? dW + (size_t)r * ld : nullptr;
+  const int grid = gridDim.x, b = blockIdx.x;
+  const int mine = b < rows ? (rows - b + grid - 1) / grid : 0;  // rows b, b+grid, ...
+  const int n2 = ld >> 1;
+  const int seg2 = (n2 + segs - 1) / segs;  // double2 per segment
+  for (int u = warp; u < mine * segs; u += kWarps) {
+    const int i = u / segs, sg = u % segs;
+    const int r = b + i * grid;
+    const int c0 = sg * seg2, c1 = min(n2, c0 + seg2);
+    double *wrow = W + (size_t)r * ld + 2 * c0;
+    double *mrow = (UPD == 2) ? dW + (size_t)r * ld + 2 * c0 : nullptr;
     const double s = UPD ? lr * ds[r] : 0.0;
-    const double z = warp_row<UPD>(wrow, mrow, xs, ld, s, alpha, lane);
-    if (lane == 0) {
-      const double y = act_kind == 0 ? act_f(z) : z;
-      for (int q = 0; q < dst.n; ++q) stg_cg(dst.p[q] + r, y);
-    }
+    const double z = c1 > c0 ? warp_row<UPD>(wrow, mrow, xs + 2 * c0, 2 * (c1 - c0), s, alpha, lane) : 0.0;
+    if (lane == 0) rowpart[i * 8 + sg] = z;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < mine; i += blockDim.x) {
+    double z = 0.0;
+    for (int sg = 0; sg < segs; ++sg) z += rowpart[i * 8 + sg];
+    const double y = act_kind == 0 ? act_f(z) : z;
+    const int r = b + i * grid;
+    for (int q = 0; q < dst.n; ++q) stg_cg(dst.p[q] + r, y);
   }
 }
 
@@ -251,7 +284,7 @@ __device__ __forceinline__ void phase_rows(double *W, double *dW, int ld, int ro
 // The CB partial sums are handed to `sink(col_in_block, value)` by threads < CB.
 // ---------------------------------------------------------------------------
 template <int CB, int UPD, typename Sink>
-__device__ __forceinline__ void col_task(double *W, double *dW, int ld, int rows, int c0, const double *ds,
+__device__ __forceinline__ void col_task(double *W, double *dW, int ld, int row_begin, int rows, int c0, const double *ds,
                                          const double *h, double lr, double alpha, double *red, Sink sink) {
   constexpr int TPR = CB / 2;          // threads per row segment (double2 each)
   constexpr int RL = kThreads / TPR;   // row lanes
@@ -304,8 +337,8 @@ __device__ __forceinline__ void col_task(double *W, double *dW, int ld, int rows
     }
   };
   // two batches of 4 rows in flight per thread (software pipeline, see warp_row)
-  load(wa, ma, rl);
-  for (int r0 = rl; r0 < rows; r0 += 8 * RL) {
+  load(wa, ma, row_begin + rl);
+  for (int r0 = row_begin + rl; r0 < rows; r0 += 8 * RL) {
     load(wb, mb, r0 + 4 * RL);
     consume(wa, ma, r0);
     load(wa, ma, r0 + 8 * RL);
@@ -333,25 +366,54 @@ __device__ __forceinline__ void col_task(double *W, double *dW, int ld, int rows
   }
 }
 
+// One task = (column block, row part): the owned rows are cut into `rsplit` contiguous parts so
+// that the task count divides evenly over the grid (512 column blocks on 148 CTAs are 3.46
+// rounds; with two row parts 6.9 -> 7 even rounds).  make_sink(c0, row_part) says where the CB
+// partial sums of that task go; the consumer adds the row parts in order.
 template <int UPD, typename SinkFactory>
-__device__ __forceinline__ void phase_cols(double *W, double *dW, int ld, int rows, int cb, const double *ds,
+__device__ __forceinline__ void phase_cols(double *W, double *dW, int ld, int rows, int cb, int rsplit, const double *ds,
                                            const double *h, double lr, double alpha, double *red,
                                            SinkFactory make_sink) {
-  const int ntasks = ld / cb;
+  const int ncb = ld / cb;
+  const int ntasks = ncb * rsplit;
+  const int part_rows = (rows + rsplit - 1) / rsplit;
   for (int t = blockIdx.x; t < ntasks; t += gridDim.x) {
-    const int c0 = t * cb;
-    auto sink = make_sink(c0);
-    if (cb == 8) col_task<8, UPD>(W, dW, ld, rows, c0, ds, h, lr, alpha, red, sink);
-    else if (cb == 16) col_task<16, UPD>(W, dW, ld, rows, c0, ds, h, lr, alpha, red, sink);
-    else col_task<32, UPD>(W, dW, ld, rows, c0, ds, h, lr, alpha, red, sink);
+    const int c0 = (t % ncb) * cb, rp = t / ncb;
+    const int rb = rp * part_rows, re = min(rows, rb + part_rows);
+    auto sink = make_sink(c0, rp);
+    if (cb == 8) col_task<8, UPD>(W, dW, ld, rb, re, c0, ds, h, lr, alpha, red, sink);
+    else if (cb == 16) col_task<16, UPD>(W, dW, ld, rb, re, c0, ds, h, lr, alpha, red, sink);
+    else col_task<32, UPD>(W, dW, ld, rb, re, c0, ds, h, lr, alpha, red, sink);
   }
 }
 
-__host__ __device__ inline int pick_col_block(int ld, int grid) {
-  if (ld % 32 == 0 && ld / 32 >= 2 * grid) return 32;
-  if (ld % 16 == 0 && ld / 16 >= 2 * grid) return 16;
-  return 8;
+struct ColPlan {
+  int cb, rsplit;
+};
+// cheapest (column block, row split) for a layer: rounds x work per task, narrow blocks
+// penalised (64-byte row segments use DRAM pages poorly), row split capped by `max_rsplit`
+__host__ __device__ inline ColPlan pick_col_plan(int ld, int rows, int grid, int max_rsplit) {
+  ColPlan best = {8, 1};
+  double best_cost = -1.0;
+  const int cbs[3] = {32, 16, 8};
+  const double pen[3] = {0.97, 1.0, 1.12};
+  for (int ci = 0; ci < 3; ++ci) {
+    const int cb = cbs[ci];
+    if (ld % cb) continue;
+    for (int rs = 1; rs <= max_rsplit; rs *= 2) {
+      if (rs > 1 && rows / rs < 256) break;
+      const long long tasks = (long long)(ld / cb) * rs;
+      const double cost = (double)((tasks + grid - 1) / grid) * cb * ((rows + rs - 1) / rs) * pen[ci];
+      if (best_cost < 0 || cost < best_cost * 0.999) {
+        best_cost = cost;
+        best.cb = cb;
+        best.rsplit = rs;
+      }
+    }
+  }
+  return best;
 }
+__host__ __device__ inline int pick_col_block(int ld, int grid) { return pick_col_plan(ld, 1 << 30, grid, 1).cb; }
 
 // ---------------------------------------------------------------------------
 // Output statistics (K-B), computed redundantly by every CTA from the gathered

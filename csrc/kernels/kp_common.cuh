@@ -6,6 +6,8 @@
 
 namespace hpnn {
 
+constexpr int kMaxRsplit = 4;  // row parts of a column task (see phase_cols)
+
 struct KP {
   hpnn_dev_net net;
   int type, train, mode, stable;

@@ -47,7 +47,8 @@ __global__ void __launch_bounds__(kThreads, 1)
            double lr, double alpha, int act_kind) {
   extern __shared__ double smem[];
   double *xs = smem;
-  double *ds = smem + ld;
+  double *rowpart = smem + ld;
+  double *ds = rowpart + row_part_doubles(rows, gridDim.x);
   stage_vec(xs, x, ld);
   if (UPD)
     for (int r = threadIdx.x; r < rows; r += blockDim.x) ds[r] = ldg_cg(delta + r);
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   Dst dst;
   dst.n = 1;
   dst.p[0] = y;
-  phase_rows<UPD>(W, dW, ld, rows, xs, ds, lr, alpha, act_kind, dst);
+  phase_rows<UPD>(W, dW, ld, rows, xs, ds, lr, alpha, act_kind, dst, pick_row_segments(rows, ld, gridDim.x), rowpart);
 }
 
 // ------------------------------- K-B ---------------------------------------
@@ -85,12 +86,12 @@ __global__ void __launch_bounds__(kThreads, 1)
   double *red = smem + ((rows + 7) & ~7);
   for (int r = threadIdx.x; r < rows; r += blockDim.x) ds[r] = ldg_cg(delta + r);
   __syncthreads();
-  auto make_sink = [=](int c0) {
+  auto make_sink = [=](int c0, int) {
     return [=](int i, double v) {
       if (c0 + i < cols) part[c0 + i] = v;
     };
   };
-  phase_cols<UPD>(W, dW, ld, rows, cb, ds, h, lr, alpha, red, make_sink);
+  phase_cols<UPD>(W, dW, ld, rows, cb, 1, ds, h, lr, alpha, red, make_sink);
 }
 
 __global__ void k_delta_finalize(const double *part, int n_parts, int stride, const double *h, int n,
@@ -220,15 +221,15 @@ int hpnn_dev_forward_layer(const double *W, int ld, int rows, int cols, const do
     set_error_msg("hpnn_dev_forward_layer: ld must be a multiple of 8");
     return -1;
   }
-  const size_t smem = sizeof(double) * ((size_t)ld + 8);
+  int grid = (rows + kWarps - 1) / kWarps;
+  if (grid > num_sms()) grid = num_sms();
+  if (grid < 1) grid = 1;
+  const size_t smem = sizeof(double) * ((size_t)ld + row_part_doubles(rows, grid) + 8);
   if (smem > 227 * 1024) {
     set_error_msg("hpnn_dev_forward_layer: input vector too long");
     return -2;
   }
   cudaFuncSetAttribute(k_rows<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  int grid = (rows + kWarps - 1) / kWarps;
-  if (grid > num_sms()) grid = num_sms();
-  if (grid < 1) grid = 1;
   k_rows<0><<<grid, kThreads, smem, (cudaStream_t)stream>>>(const_cast<double *>(W), nullptr, ld, rows, x,
                                                             nullptr, y, 0.0, 0.0, act_kind);
   HPNN_CHECK_LAUNCH("k_rows<0>");
@@ -243,14 +244,14 @@ int hpnn_dev_update_forward(double *W, double *dW, int ld, int rows, int cols, c
     set_error_msg("hpnn_dev_update_forward: bad arguments");
     return -1;
   }
-  const size_t smem = sizeof(double) * ((size_t)ld + ((rows + 7) & ~7) + 8);
+  int grid = (rows + kWarps - 1) / kWarps;
+  if (grid > num_sms()) grid = num_sms();
+  if (grid < 1) grid = 1;
+  const size_t smem = sizeof(double) * ((size_t)ld + ((rows + 7) & ~7) + row_part_doubles(rows, grid) + 8);
   if (smem > 227 * 1024) {
     set_error_msg("hpnn_dev_update_forward: layer too wide");
     return -2;
   }
-  int grid = (rows + kWarps - 1) / kWarps;
-  if (grid > num_sms()) grid = num_sms();
-  if (grid < 1) grid = 1;
   cudaStream_t s = (cudaStream_t)stream;
   if (update == 0) {
     cudaFuncSetAttribute(k_rows<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

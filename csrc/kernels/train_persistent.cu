@@ -22,12 +22,19 @@
 namespace hpnn {
 
 // delta_l[r] = dact(h_l[r]) * sum_g part_l[g][r] for the owned rows, into shared memory
-__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, const double *act_next, double *ds) {
+// column-task plan of layer l; computed from the LARGEST row slice so that every rank agrees
+__device__ __forceinline__ ColPlan layer_plan(const hpnn_dev_net &n, int l, int grid) {
+  return pick_col_plan(n.ld[l], (n.dims[l + 1] + n.world - 1) / n.world, grid, kMaxRsplit);
+}
+
+// (rank g, row part rp of the producing layer) lives in slot g*kMaxRsplit + rp
+__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, int rsplit, const double *act_next, double *ds) {
   const double *part = n.arena[n.rank] + n.off_part[l];
   const int stride = n.part_stride[l];
   for (int r = threadIdx.x; r < n.rows[l]; r += blockDim.x) {
     double s = 0.0;
-    for (int g = 0; g < n.world; ++g) s += ldg_cg(part + (size_t)g * stride + r);
+    for (int g = 0; g < n.world; ++g)
+      for (int rp = 0; rp < rsplit; ++rp) s += ldg_cg(part + (size_t)(g * kMaxRsplit + rp) * stride + r);
     ds[r] = s * dact_f(ldg_cg(act_next + n.row0[l] + r));
   }
 }
@@ -37,6 +44,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   double *xs = smem;
   double *ds = xs + p.max_ld;
   double *red = ds + p.max_rows;
+  double *rowpart = red + kRedDoubles;
 
   const hpnn_dev_net &n = p.net;
   const int NL = n.n_layers;
@@ -70,9 +78,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     dst.n = n.world;
     for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + n.row0[l];
     const int kind = (snn && l == NL - 1) ? 1 : 0;
-    if (u == 0) phase_rows<0>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, 0.0, 0.0, kind, dst);
-    else if (u == 1) phase_rows<1>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst);
-    else phase_rows<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst);
+    const int segs = pick_row_segments(n.rows[l], n.ld[l], gridDim.x);
+    if (u == 0) phase_rows<0>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, 0.0, 0.0, kind, dst, segs, rowpart);
+    else if (u == 1) phase_rows<1>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst, segs, rowpart);
+    else phase_rows<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst, segs, rowpart);
   };
 
   // ---- prologue: zero the momentum (per sample, src/ann.c:2386), first forward
@@ -104,33 +113,35 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
       // ---- top-down: deltas from the old weights fused with the update
       for (int l = last; l >= 1; --l) {
         if (l != last) {
-          stage_delta(n, l, act_of(n.rank, l + 1, cur), ds);
+          stage_delta(n, l, layer_plan(n, l + 1, grid).rsplit,
+                      act_of(n.rank, l + 1, cur), ds);
           __syncthreads();
         }
         const int cols = n.dims[l];
-        const int cb = pick_col_block(n.ld[l], grid);
+        const ColPlan plan = layer_plan(n, l, grid);
+        const int cb = plan.cb;
         const long long off_prev = n.off_part[l - 1];
         const int stride_prev = n.part_stride[l - 1];
-        auto make_sink = [&](int c0) {
+        auto make_sink = [&](int c0, int rp) {
           return [=, &n](int i, double v) {
             const int col = c0 + i;
             if (col < cols) {
               const int own = owner_of_row(col, cols, n.world);
-              double *dstp = n.arena[own] + off_prev + (size_t)n.rank * stride_prev +
+              double *dstp = n.arena[own] + off_prev + (size_t)(n.rank * kMaxRsplit + rp) * stride_prev +
                              (col - row0_of(own, cols, n.world));
               stg_cg(dstp, v);
             }
           };
         };
         const double *h = act_of(n.rank, l, cur);
-        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, ds, h, p.lr, p.alpha, red, make_sink);
-        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, ds, h, p.lr, p.alpha, red, make_sink);
+        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, p.lr, p.alpha, red, make_sink);
+        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, p.lr, p.alpha, red, make_sink);
         trace(100 + l);
-        bar.sync_all(n, (int)blockIdx.x < n.ld[l] / cb);
+        bar.sync_all(n, (int)blockIdx.x < (n.ld[l] / cb) * plan.rsplit);
         trace(200 + l);
       }
       // ---- bottom-up: layer 0 update fused with its forward, then the rest
-      stage_delta(n, 0, act_of(n.rank, 1, cur), ds);
+      stage_delta(n, 0, layer_plan(n, 1, grid).rsplit, act_of(n.rank, 1, cur), ds);
       forward_layer(0, 0, cur ^ 1, upd);
       trace(300);
       bar.sync_all(n, (int)blockIdx.x < n.rows[0]);
@@ -236,7 +247,7 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
   }
   for (int l = 0; l < NL; ++l) {
     net->off_part[l] = off;
-    off += (long long)W * net->part_stride[l];
+    off += (long long)W * kMaxRsplit * net->part_stride[l];  // slot (rank, row part)
   }
   net->off_target = off;
   off += pad(net->dims[NL]);
@@ -302,7 +313,12 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
       return rc;
     }
   }
-  const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles);
+  int rowpart = 8;
+  for (int l = 0; l < net->n_layers; ++l) {
+    const int d = row_part_doubles(net->rows[l], grid);
+    rowpart = d > rowpart ? d : rowpart;
+  }
+  const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles + rowpart);
   if (smem > 227 * 1024) {
     set_error_msg("hpnn_dev_train_sample: layer too wide for the persistent kernel (use the multi-launch path)");
     return -2;
