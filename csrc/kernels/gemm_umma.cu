@@ -6,12 +6,12 @@
 // this kernel is never used for parity: it serves `run_nn --batch` / HpnnNet.forward_batch with
 // precision="bf16".  Structure (one 128x128 output tile per CTA, 192 threads):
 //   warp 0      TMA producer: cp.async.bulk.tensor (128B-swizzled 128x64 bf16 boxes of X and W)
-//               into a 4-stage shared-memory ring, completion on mbarriers;
+//               into a 3-stage shared-memory ring, completion on mbarriers;
 //   warp 1      allocates 128 TMEM columns, one elected lane issues tcgen05.mma (M=128, N=128,
 //               K=16, kind::f16, fp32 accumulate in TMEM); tcgen05.commit frees ring slots and
 //               finally signals the epilogue;
 //   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction), activation in
-//               FP64, direct stores of the FP64 result.
+//               fp32 (the operands were bf16 anyway), direct stores widened to FP64.
 // Out-of-range rows/columns of partial tiles are zero-filled by TMA and masked at the store.
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -30,7 +30,8 @@ namespace umma {
 
 constexpr int BM = 128, BN = 128, BK = 64;       // tile (BK bf16 = one 128-byte swizzle row)
 constexpr int UMMA_K = 16;                       // bf16 MMA depth
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;                        // 3 x 32 KB: two CTAs fit one SM, so one CTA's
+                                                 // epilogue overlaps the other's MMA main loop
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;   // 32 KB
 constexpr int TMEM_COLS = 128;
@@ -106,7 +107,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 // instruction descriptor: D=f32, A=B=bf16, both K-major, N=128, M=128
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 2)
     k_gemm_bf16_umma(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w, int batch,
                      int rows, int k_total, double *__restrict__ Y, int ldy, int act_kind) {
   extern __shared__ uint8_t smem_raw[];
@@ -186,8 +187,9 @@ __global__ void __launch_bounds__(THREADS, 1)
         for (int j = 0; j < 32; ++j) {
           const int n = n0 + c0 + j;
           if (n < rows) {
-            const double z = (double)__uint_as_float(v[j]);
-            yrow[n] = act_kind == 0 ? act_f(z) : z;
+            // reduced-precision path: the activation is evaluated in fp32 (operands were bf16)
+            const float z = __uint_as_float(v[j]);
+            yrow[n] = (double)(act_kind == 0 ? __fdividef(2.0f, 1.0f + __expf(-z)) - 1.0f : z);
           }
         }
       }

@@ -9,6 +9,7 @@
 //   k_backward_update  cublasDgemv(OP_N)+dsigmoid / dsigmoid_mul_delta_T + cublasDger /
 //                      ger_acc / Dger+Daxpy+Dscal / ger_dw_acc   cuda_ann.cu:1447-1453,2139,3155-3165
 //   k_update_forward   ger_acc|ger_dw_acc followed by fw_mv_acc  cuda_ann.cu:124-148,77-86
+#include <stdint.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -104,54 +105,91 @@ __global__ void k_delta_finalize(const double *part, int n_parts, int stride, co
 }
 
 // ------------------------------- K-G (fp64) ---------------------------------
-// Y[b, r] = f( sum_c X[b, c] * W[r, c] ): classic 64x64x16 shared-memory tiling with
-// a 4x4 register block per thread (256 threads).  FP64 FMA pipe; the reference has
-// no batched path at all (batch = 1), so this is measured against
-// B x its single-sample time.
-constexpr int GB = 64, GK = 16;
-__global__ void __launch_bounds__(256)
+// Y[b, r] = f( sum_c X[b, c] * W[r, c] ) in FP64.  tcgen05 has no FP64 kind, so the FP64 tensor
+// path is the warp-level DMMA (mma.sync.m8n8k4.f64): 64x64 output tile per CTA, 4 warps, each
+// warp a 32x32 sub-tile = 4x4 DMMA tiles; operands stay K-major in shared memory exactly as they
+// are in global memory (both X and W are row-major with K contiguous), staged by a double-
+// buffered cp.async pipeline with a 20-double row pitch (conflict-free fragment loads).
+// The reference has no batched path (batch = 1); measured against cuBLAS DGEMM.
+constexpr int GB = 64, GK = 16, GP = 20;  // tile, k-slab, shared row pitch (doubles)
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem, bool valid) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  const int bytes = valid ? 16 : 0;  // src-size 0 => zero fill
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void dmma_m8n8k4(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c[0]), "+d"(c[1])
+               : "d"(a), "d"(b));
+}
+__global__ void __launch_bounds__(128)
     k_forward_batch_f64(const double *__restrict__ W, int ld, int rows, int cols, const double *__restrict__ X,
                         int ldx, int batch, double *__restrict__ Y, int ldy, int act_kind) {
-  __shared__ double Xs[GK][GB + 1];
-  __shared__ double Ws[GK][GB + 1];
+  __shared__ __align__(16) double Xs[2][GB][GP];
+  __shared__ __align__(16) double Ws[2][GB][GP];
   const int b0 = blockIdx.y * GB, r0 = blockIdx.x * GB;
-  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;  // tx -> rows (N), ty -> batch
-  double acc[4][4] = {};
-  for (int k0 = 0; k0 < cols; k0 += GK) {
-    // 64x16 tiles of X and W: 1024 elements each, 4 per thread
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;  // warp sub-tile origin (batch, rows)
+  const int g = lane >> 2, q = lane & 3;                    // DMMA fragment coordinates
+  double acc[4][4][2] = {};
+  // stage one 64x16 slab of X and W: 64 rows x 8 chunks of 16 B each, 4 chunks per thread per matrix
+  auto stage = [&](int buf, int k0) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const int e = threadIdx.x + 256 * i;
-      const int kk = e % GK, mm = e / GK;
-      const int c = k0 + kk;
-      Xs[kk][mm] = (b0 + mm < batch && c < cols) ? X[(size_t)(b0 + mm) * ldx + c] : 0.0;
-      Ws[kk][mm] = (r0 + mm < rows && c < cols) ? W[(size_t)(r0 + mm) * ld + c] : 0.0;
+      const int e = threadIdx.x + 128 * i;
+      const int m = e >> 3, c = (e & 7) * 2;
+      const bool kin = k0 + c < cols, kin2 = k0 + c + 1 < cols;
+      double *xs = &Xs[buf][m][c], *ws = &Ws[buf][m][c];
+      if (kin && !kin2) {  // odd tail column: plain stores, no async copy may touch this chunk
+        xs[0] = (b0 + m < batch) ? X[(size_t)(b0 + m) * ldx + k0 + c] : 0.0;
+        xs[1] = 0.0;
+        ws[0] = (r0 + m < rows) ? W[(size_t)(r0 + m) * ld + k0 + c] : 0.0;
+        ws[1] = 0.0;
+      } else {             // whole chunk in range, or whole chunk zero-filled
+        cp_async16(xs, X + (size_t)(b0 + m) * ldx + k0 + c, kin && (b0 + m < batch));
+        cp_async16(ws, W + (size_t)(r0 + m) * ld + k0 + c, kin && (r0 + m < rows));
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const int nk = (cols + GK - 1) / GK;
+  stage(0, 0);
+  for (int kb = 0; kb < nk; ++kb) {
+    const int buf = kb & 1;
+    if (kb + 1 < nk) {
+      stage(buf ^ 1, (kb + 1) * GK);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
 #pragma unroll
-    for (int kk = 0; kk < GK; ++kk) {
-      double xv[4], wv[4];
+    for (int kk = 0; kk < GK; kk += 4) {
+      double a[4], b[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        xv[i] = Xs[kk][ty + 16 * i];
-        wv[i] = Ws[kk][tx + 16 * i];
+        a[i] = Xs[buf][wm + 8 * i + g][kk + q];  // A[m = g][k = q]   (row-major 8x4)
+        b[i] = Ws[buf][wn + 8 * i + g][kk + q];  // B[k = q][n = g]   (col-major 4x8)
       }
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fma(xv[i], wv[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) dmma_m8n8k4(acc[i][j], a[i], b[j]);
     }
     __syncthreads();
   }
+  // C fragment: lane holds C[m = g][n = 2q], C[m = g][n = 2q + 1]
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int b = b0 + ty + 16 * i;
+    const int b = b0 + wm + 8 * i + g;
     if (b >= batch) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int r = r0 + tx + 16 * j;
-      if (r < rows) Y[(size_t)b * ldy + r] = act_kind == 0 ? act_f(acc[i][j]) : acc[i][j];
-    }
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int r = r0 + wn + 8 * j + 2 * q + e;
+        if (r < rows) Y[(size_t)b * ldy + r] = act_kind == 0 ? act_f(acc[i][j][e]) : acc[i][j][e];
+      }
   }
 }
 
@@ -321,8 +359,12 @@ int hpnn_dev_delta_finalize(const double *part, int n_parts, int stride, const d
 
 int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
                                double *Y, int ldy, int act_kind, void *stream) {
+  if ((ld & 1) || (ldx & 1) || ((uintptr_t)W & 15) || ((uintptr_t)X & 15)) {
+    set_error_msg("hpnn_dev_forward_batch_f64: W and X need 16-byte aligned rows (even leading dimensions)");
+    return -1;
+  }
   dim3 grid((rows + GB - 1) / GB, (batch + GB - 1) / GB);
-  k_forward_batch_f64<<<grid, 256, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, Y, ldy, act_kind);
+  k_forward_batch_f64<<<grid, 128, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, Y, ldy, act_kind);
   HPNN_CHECK_LAUNCH("k_forward_batch_f64");
   return 0;
 }

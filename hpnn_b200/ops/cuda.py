@@ -107,9 +107,12 @@ def forward_batch(Wp: torch.Tensor, cols: int, X: torch.Tensor, act_kind: int = 
     "bf16" (opt-in: tcgen05 tensor cores, fp32 accumulation in TMEM)."""
     lib = N.load()
     rows, ld = Wp.shape
-    X = X.contiguous()
     B = X.shape[0]
-    Y = torch.empty((B, rows), dtype=torch.float64, device=Wp.device)
+    if X.stride(1) != 1 or X.stride(0) % 2 or X.data_ptr() % 16:  # 16-byte aligned rows for cp.async / TMA
+        Xa = torch.zeros((B, (X.shape[1] + 7) & ~7), dtype=torch.float64, device=Wp.device)
+        Xa[:, : X.shape[1]].copy_(X)
+        X = Xa
+    Y = torch.empty((B, (rows + 7) & ~7), dtype=torch.float64, device=Wp.device)[:, :rows]
     if precision == "fp64":
         N.check(lib.hpnn_dev_forward_batch_f64(Wp.data_ptr(), ld, rows, cols, X.data_ptr(), X.stride(0), B,
                                                Y.data_ptr(), Y.stride(0), act_kind, _s()),
