@@ -122,9 +122,15 @@ __device__ __forceinline__ void dmma_m8n8k4(double (&c)[2], double a, double b) 
                : "+d"(c[0]), "+d"(c[1])
                : "d"(a), "d"(b));
 }
+// where the output tile goes: the same [batch x ldy] matrix on up to HPNN_MAX_WORLD ranks,
+// columns shifted by col0 (this rank's row slice of the layer) -- all-gather by peer stores
+struct GemmDst {
+  double *y[HPNN_MAX_WORLD];
+  int n, col0;
+};
 __global__ void __launch_bounds__(128)
     k_forward_batch_f64(const double *__restrict__ W, int ld, int rows, int cols, const double *__restrict__ X,
-                        int ldx, int batch, double *__restrict__ Y, int ldy, int act_kind) {
+                        int ldx, int batch, GemmDst dst, int ldy, int act_kind) {
   __shared__ __align__(16) double Xs[2][GB][GP];
   __shared__ __align__(16) double Ws[2][GB][GP];
   const int b0 = blockIdx.y * GB, r0 = blockIdx.x * GB;
@@ -188,7 +194,10 @@ __global__ void __launch_bounds__(128)
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int r = r0 + wn + 8 * j + 2 * q + e;
-        if (r < rows) Y[(size_t)b * ldy + r] = act_kind == 0 ? act_f(acc[i][j][e]) : acc[i][j][e];
+        if (r < rows) {
+          const double y = act_kind == 0 ? act_f(acc[i][j][e]) : acc[i][j][e];
+          for (int p = 0; p < dst.n; ++p) dst.y[p][(size_t)b * ldy + dst.col0 + r] = y;
+        }
       }
   }
 }
@@ -364,8 +373,59 @@ int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, cons
     return -1;
   }
   dim3 grid((rows + GB - 1) / GB, (batch + GB - 1) / GB);
-  k_forward_batch_f64<<<grid, 128, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, Y, ldy, act_kind);
+  GemmDst dst;
+  dst.n = 1;
+  dst.col0 = 0;
+  dst.y[0] = Y;
+  k_forward_batch_f64<<<grid, 128, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, dst, ldy, act_kind);
   HPNN_CHECK_LAUNCH("k_forward_batch_f64");
+  return 0;
+}
+
+// Row-split layer: this rank computes its `rows` neurons for the whole batch and the epilogue
+// stores the tile into every rank's [batch x ldy] activation matrix at column col0 (GEMM fused
+// with the all-gather of its result over NVLink peer memory).
+int hpnn_dev_forward_batch_f64_tp(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
+                                  double *const *Y_all, int n_ranks, int col0, int ldy, int act_kind, void *stream) {
+  if ((ld & 1) || (ldx & 1) || ((uintptr_t)W & 15) || ((uintptr_t)X & 15) || n_ranks < 1 || n_ranks > HPNN_MAX_WORLD) {
+    set_error_msg("hpnn_dev_forward_batch_f64_tp: bad arguments");
+    return -1;
+  }
+  if (rows <= 0) return 0;
+  GemmDst dst;
+  dst.n = n_ranks;
+  dst.col0 = col0;
+  for (int p = 0; p < HPNN_MAX_WORLD; ++p) dst.y[p] = p < n_ranks ? Y_all[p] : nullptr;
+  dim3 grid((rows + GB - 1) / GB, (batch + GB - 1) / GB);
+  k_forward_batch_f64<<<grid, 128, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, dst, ldy, act_kind);
+  HPNN_CHECK_LAUNCH("k_forward_batch_f64(tp)");
+  return 0;
+}
+
+// Cross-rank barrier as a one-CTA kernel (every rank launches it on its own GPU): fence.sys,
+// publish `epoch` in every peer's flag word, wait for all peers' words.  flags[p] is rank p's
+// flag array (HPNN_MAX_WORLD u64) as mapped here.
+struct FlagPtrs {
+  unsigned long long *p[HPNN_MAX_WORLD];
+};
+__global__ void k_world_barrier_v(FlagPtrs f, int rank, int world, unsigned long long epoch) {
+  if (threadIdx.x == 0) fence_sys();
+  __syncthreads();
+  if ((int)threadIdx.x < world && (int)threadIdx.x != rank) {
+    st_relaxed_sys(f.p[threadIdx.x] + rank, epoch);
+    while (ld_relaxed_sys(f.p[rank] + threadIdx.x) < epoch) {
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) fence_sys();
+}
+int hpnn_dev_world_barrier(void *const *flags_all, int rank, int world, unsigned long long epoch, void *stream) {
+  if (world < 1 || world > HPNN_MAX_WORLD) return -1;
+  if (world == 1) return 0;
+  FlagPtrs f;
+  for (int p = 0; p < HPNN_MAX_WORLD; ++p) f.p[p] = p < world ? (unsigned long long *)flags_all[p] : nullptr;
+  k_world_barrier_v<<<1, 32, 0, (cudaStream_t)stream>>>(f, rank, world, epoch);
+  HPNN_CHECK_LAUNCH("k_world_barrier");
   return 0;
 }
 

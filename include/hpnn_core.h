@@ -229,6 +229,13 @@ int hpnn_dev_update_forward(double *W, double *dW, int ld, int rows, int cols, c
 /* batched inference (extension): Y[B x N] = f(X[B x M] . W^T), fp64 */
 int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, const double *X, int ldx,
                                int batch, double *Y, int ldy, int act_kind, void *stream);
+/* row-split layer of a batched forward: GEMM whose epilogue stores the result into EVERY rank's
+ * activation matrix at column col0 (all-gather over NVLink peer memory fused into the GEMM),
+ * and the one-CTA cross-rank barrier that separates two such layers.  Y_all[p] / flags_all[p]
+ * are rank p's buffers as mapped into this process; epoch must grow by one per call. */
+int hpnn_dev_forward_batch_f64_tp(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
+                                  double *const *Y_all, int n_ranks, int col0, int ldy, int act_kind, void *stream);
+int hpnn_dev_world_barrier(void *const *flags_all, int rank, int world, unsigned long long epoch, void *stream);
 /* opt-in reduced precision (K-T): bf16 operands, fp32 accumulation on the tcgen05 tensor cores
  * (TMA -> shared memory -> tcgen05.mma -> TMEM -> epilogue), FP64 result.  Never used for parity.
  * hpnn_dev_cast_bf16 converts an fp64 matrix (zero-filling up to ld_dst); Wb/Xb must be 16-byte

@@ -101,6 +101,28 @@ def main():
     if not (e_ab < 1e-13 and e_as < 1e-13):
         fails += 1
     a.close(); b.close()
+    # ---- batched inference on the row-split net: fused GEMM+all-gather == NCCL == single-rank
+    from hpnn_b200.models.net import HpnnNet
+    from hpnn_b200.parallel.tp import TPBatchRunner, forward_batch_parallel
+
+    for nn_type in (N.TYPE_ANN, N.TYPE_SNN):
+        k, _ = hp.generate_kernel(9, 101, [67, 45], 11)
+        Xb = torch.from_numpy(np.random.default_rng(4).random((300, 101))).cuda()
+        tpnet = HpnnNet(k, nn_type, momentum=False, group=group)
+        full = HpnnNet(k, nn_type, momentum=False)
+        runner = TPBatchRunner(tpnet, max_batch=512)
+        ref_out = full.forward_batch(Xb)
+        yf = runner.forward(Xb, "fused")
+        yn = runner.forward(Xb, "nccl")
+        yf2 = runner.forward(Xb, "fused")
+        yb = forward_batch_parallel(full, Xb, group=group)
+        errs = [float((y - ref_out).abs().max()) for y in (yf, yn, yf2, yb)]
+        if rank == 0:
+            print(f"case tp-batch type={nn_type} world={world}: max|fused-ref|={errs[0]:.2e} nccl={errs[1]:.2e} "
+                  f"fused again={errs[2]:.2e} batch-parallel={errs[3]:.2e}", flush=True)
+        if max(errs) > 1e-12:
+            fails += 1
+        runner.close(); tpnet.close(); full.close()
     flag = torch.tensor([fails], device="cuda")
     dist.all_reduce(flag)
     if rank == 0:
