@@ -96,6 +96,14 @@ Shim *wrap(hpnn_kernel *h) {
   for (int l = 0; l < NL; ++l)
     cpu_bytes += sizeof(double) * ((unsigned long)hpnn_kernel_dim(h, l) + 1) * hpnn_kernel_dim(h, l + 1);
   NN_OUT(stdout, "[CPU] ANN total allocation: %lu (bytes)\n", cpu_bytes);
+  if (use_device()) {
+    // reported here, like the reference does at allocation time (src/ann.c:197-200); the device
+    // copy itself is created on first use: padded rows + activation / partial buffers
+    unsigned long gpu_bytes = 0;
+    for (int l = 0; l < NL; ++l)
+      gpu_bytes += sizeof(double) * (unsigned long)((hpnn_kernel_dim(h, l) + 7) & ~7) * hpnn_kernel_dim(h, l + 1);
+    NN_OUT(stdout, "[GPU] ANN total allocation: %lu (bytes)\n", gpu_bytes);
+  }
   return s;
 }
 
@@ -129,7 +137,6 @@ hpnn_net *device_for(Shim *s, int type, bool momentum) {
     }
     s->dev_momentum = momentum;
     s->dev_gpus = want_gpus;
-    NN_OUT(stdout, "[GPU] ANN total allocation: %lu (bytes)\n", (unsigned long)hpnn_net_device_bytes(s->dev));
   } else if (s->dev_stale) {
     hpnn_net_upload(s->dev, s->host);
   }
