@@ -150,7 +150,18 @@ __device__ __forceinline__ void stage_vec(double *dst, const double *src, int n)
 struct Dst {
   double *p[HPNN_MAX_WORLD];
   int n;
+  unsigned long long tag;  // != 0: publish {value, tag} pairs (tagged hand-over, see kp_common.cuh)
 };
+__device__ __forceinline__ void dst_store(const Dst &dst, int r, double y) {
+  for (int q = 0; q < dst.n; ++q) {
+    if (dst.tag)
+      asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};" ::"l"(dst.p[q] + 2 * (size_t)r),
+                   "l"(__double_as_longlong(y)), "l"(dst.tag)
+                   : "memory");
+    else
+      stg_cg(dst.p[q] + r, y);
+  }
+}
 
 // ---------------------------------------------------------------------------
 // Row tasks (K-A / K-D / K-E): one warp per owned row.
@@ -273,7 +284,7 @@ __device__ __forceinline__ void phase_rows(double *W, double *dW, int ld, int ro
     for (int sg = 0; sg < segs; ++sg) z += rowpart[i * 8 + sg];
     const double y = act_kind == 0 ? act_f(z) : z;
     const int r = b + i * grid;
-    for (int q = 0; q < dst.n; ++q) stg_cg(dst.p[q] + r, y);
+    dst_store(dst, r, y);
   }
 }
 
@@ -285,15 +296,15 @@ __device__ __forceinline__ void phase_rows(double *W, double *dW, int ld, int ro
 // ---------------------------------------------------------------------------
 template <int CB, int UPD, typename Sink>
 __device__ __forceinline__ void col_task(double *W, double *dW, int ld, int row_begin, int rows, int c0, const double *ds,
-                                         const double *h, double lr, double alpha, double *red, Sink sink) {
+                                         const double *h, bool h_shared, double lr, double alpha, double *red, Sink sink) {
   constexpr int TPR = CB / 2;          // threads per row segment (double2 each)
   constexpr int RL = kThreads / TPR;   // row lanes
   const int cp = threadIdx.x % TPR, rl = threadIdx.x / TPR;
   const int c = c0 + 2 * cp;
   double h0 = 0.0, h1 = 0.0;
   if (UPD) {
-    h0 = ldg_cg(h + c);
-    h1 = ldg_cg(h + c + 1);
+    h0 = h_shared ? h[c] : ldg_cg(h + c);
+    h1 = h_shared ? h[c + 1] : ldg_cg(h + c + 1);
   }
   double a0 = 0.0, a1 = 0.0;
   const size_t stride2 = (size_t)(ld >> 1);
@@ -372,7 +383,7 @@ __device__ __forceinline__ void col_task(double *W, double *dW, int ld, int row_
 // partial sums of that task go; the consumer adds the row parts in order.
 template <int UPD, typename SinkFactory>
 __device__ __forceinline__ void phase_cols(double *W, double *dW, int ld, int rows, int cb, int rsplit, const double *ds,
-                                           const double *h, double lr, double alpha, double *red,
+                                           const double *h, bool h_shared, double lr, double alpha, double *red,
                                            SinkFactory make_sink) {
   const int ncb = ld / cb;
   const int ntasks = ncb * rsplit;
@@ -381,9 +392,9 @@ __device__ __forceinline__ void phase_cols(double *W, double *dW, int ld, int ro
     const int c0 = (t % ncb) * cb, rp = t / ncb;
     const int rb = rp * part_rows, re = min(rows, rb + part_rows);
     auto sink = make_sink(c0, rp);
-    if (cb == 8) col_task<8, UPD>(W, dW, ld, rb, re, c0, ds, h, lr, alpha, red, sink);
-    else if (cb == 16) col_task<16, UPD>(W, dW, ld, rb, re, c0, ds, h, lr, alpha, red, sink);
-    else col_task<32, UPD>(W, dW, ld, rb, re, c0, ds, h, lr, alpha, red, sink);
+    if (cb == 8) col_task<8, UPD>(W, dW, ld, rb, re, c0, ds, h, h_shared, lr, alpha, red, sink);
+    else if (cb == 16) col_task<16, UPD>(W, dW, ld, rb, re, c0, ds, h, h_shared, lr, alpha, red, sink);
+    else col_task<32, UPD>(W, dW, ld, rb, re, c0, ds, h, h_shared, lr, alpha, red, sink);
   }
 }
 

@@ -16,6 +16,8 @@
 // => 2*NL-1 barriers and 3 passes over W (5 with momentum) per iteration, against the
 // reference's ~3*NL+4 device-wide syncs and 5 (9) passes.
 #include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "kp_common.cuh"
 
@@ -28,17 +30,41 @@ __device__ __forceinline__ ColPlan layer_plan(const hpnn_dev_net &n, int l, int 
 }
 
 // (rank g, row part rp of the producing layer) lives in slot g*kMaxRsplit + rp
-__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, int rsplit, const double *act_next, double *ds) {
+// tagged: partials and activations are {value, tag} pairs; the partials are polled until `tag`
+__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, int rsplit, const double *act_next, double *ds,
+                                            bool tagged, unsigned long long tag) {
   const double *part = n.arena[n.rank] + n.off_part[l];
   const int stride = n.part_stride[l];
+  const int combos = n.world * rsplit;  // (rank, row part) slots, summed rank-major
   for (int r = threadIdx.x; r < n.rows[l]; r += blockDim.x) {
     double s = 0.0;
-    for (int g = 0; g < n.world; ++g)
-      for (int rp = 0; rp < rsplit; ++rp) s += ldg_cg(part + (size_t)(g * kMaxRsplit + rp) * stride + r);
-    ds[r] = s * dact_f(ldg_cg(act_next + n.row0[l] + r));
+    if (tagged) {
+      for (int c0 = 0; c0 < combos; c0 += 8) {  // 8 polls in flight
+        const double *addr[8];
+        bool want[8];
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = c0 + u;
+          want[u] = c < combos;
+          const int g = want[u] ? c / rsplit : 0, rp = want[u] ? c % rsplit : 0;
+          addr[u] = part + 2 * ((size_t)(g * kMaxRsplit + rp) * stride + r);
+        }
+        ld_pairs_wait<8, false>(addr, want, tag, v);  // local arena: GPU-scope loads see the peers' stores
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s += v[u];
+      }
+    } else {
+      for (int g = 0; g < n.world; ++g)
+        for (int rp = 0; rp < rsplit; ++rp) s += ldg_cg(part + (size_t)(g * kMaxRsplit + rp) * stride + r);
+    }
+    const size_t hidx = (size_t)(n.row0[l] + r) * (tagged ? 2 : 1);  // own output of the previous sweep
+    ds[r] = s * dact_f(ldg_cg(act_next + hidx));
   }
 }
 
+// TG: tagged-pair hand-over between ranks (world > 1); false = plain buffers + barriers
+template <bool TG>
 __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_constant__ KP p) {
   extern __shared__ double smem[];
   double *xs = smem;
@@ -56,6 +82,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
 
   Barrier bar;
   bar.init(n);
+  // Several ranks: every vector that crosses NVLink is handed over as tagged pairs (no fences,
+  // no cross-rank barrier); grid barriers stay local to the GPU.  p.tagged == 0 keeps the
+  // fence + flag-word barrier (one rank, or HPNN_TP_PROTOCOL=barrier).
+  constexpr bool tg = TG;
+  const unsigned long long launch = (unsigned long long)ld_relaxed_gpu(n.local_sync + 160) + 1ull;
+  auto tag_of = [&](int iteration) { return (launch << 32) | (unsigned long long)(unsigned)iteration; };
+  auto sync_phase = [&](bool remote) {
+    if (tg) bar.sync_local();
+    else bar.sync_all(n, remote);
+  };
   int trace_n = 0;
   auto trace = [&](int tag) {
     if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
@@ -68,15 +104,21 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   // act[i], i >= 1, is double buffered: the fused update+forward of layer 0 rewrites
   // act[1] while other CTAs may still need the old values to finish delta_0.
   int cur = 0;
-  auto act_of = [&](int rank, int i, int buf) -> double * {
-    return n.arena[rank] + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]));
+  auto act_of = [&](int rank, int i, int buf) -> double * {  // tagged mode: a buffer holds pairs
+    return n.arena[rank] + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]) * (tg ? 2 : 1));
   };
-  auto forward_layer = [&](int l, int src_buf, int dst_buf, int u) {
-    stage_vec(xs, act_of(n.rank, l, src_buf), n.ld[l]);
+  // input vector of layer l (act[l], buffer src_buf) into shared memory
+  auto stage_act = [&](double *dst_smem, int i, int buf, unsigned long long tag) {
+    if (tg && i > 0) stage_pairs<false>(dst_smem, act_of(n.rank, i, buf), n.dims[i], pad8(n.dims[i]), tag);
+    else stage_vec(dst_smem, act_of(n.rank, i, buf), pad8(n.dims[i]));
+  };
+  auto forward_layer = [&](int l, int src_buf, int dst_buf, int u, unsigned long long tag) {
+    stage_act(xs, l, src_buf, tag);
     __syncthreads();
     Dst dst;
     dst.n = n.world;
-    for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + n.row0[l];
+    dst.tag = tg ? tag : 0ull;
+    for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + (size_t)n.row0[l] * (tg ? 2 : 1);
     const int kind = (snn && l == NL - 1) ? 1 : 0;
     const int segs = pick_row_segments(n.rows[l], n.ld[l], gridDim.x);
     if (u == 0) phase_rows<0>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, 0.0, 0.0, kind, dst, segs, rowpart);
@@ -94,13 +136,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     }
   }
   for (int l = 0; l < NL; ++l) {
-    forward_layer(l, cur, cur, 0);
-    bar.sync_all(n, (int)blockIdx.x < n.rows[l]);
+    forward_layer(l, cur, cur, 0, tag_of(0));
+    sync_phase((int)blockIdx.x < n.rows[l]);
   }
   const double *target = A + n.off_target;
   const int last = NL - 1;
-  OutStats st = output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, n.row0[last],
-                             n.rows[last], ds, (p.mode == 1 && blockIdx.x == 0) ? A + n.off_out : nullptr, red);
+  // output statistics from the gathered output vector (tagged mode: gathered into xs first)
+  auto evaluate = [&](unsigned long long tag, int row0, int rows, double *dsp, double *o_out) -> OutStats {
+    if (tg) {
+      __syncthreads();
+      stage_act(xs, NL, cur, tag);
+      __syncthreads();
+      return output_stats<true>(p.type, p.stable, xs, target, n_out, row0, rows, dsp, o_out, red);
+    }
+    return output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, row0, rows, dsp, o_out, red);
+  };
+  OutStats st = evaluate(tag_of(0), n.row0[last], n.rows[last], ds,
+                         (p.mode == 1 && blockIdx.x == 0) ? A + n.off_out : nullptr);
   double E = st.err;
   const double init_err = E;
   int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
@@ -110,11 +162,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     for (;;) {
       ++iter;
       trace(1);
+      const unsigned long long tag = tag_of(iter);
       // ---- top-down: deltas from the old weights fused with the update
       for (int l = last; l >= 1; --l) {
         if (l != last) {
-          stage_delta(n, l, layer_plan(n, l + 1, grid).rsplit,
-                      act_of(n.rank, l + 1, cur), ds);
+          stage_delta(n, l, layer_plan(n, l + 1, grid).rsplit, act_of(n.rank, l + 1, cur), ds, tg, tag);
           __syncthreads();
         }
         const int cols = n.dims[l];
@@ -127,35 +179,39 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
             const int col = c0 + i;
             if (col < cols) {
               const int own = owner_of_row(col, cols, n.world);
-              double *dstp = n.arena[own] + off_prev + (size_t)(n.rank * kMaxRsplit + rp) * stride_prev +
-                             (col - row0_of(own, cols, n.world));
-              stg_cg(dstp, v);
+              const size_t slot = (size_t)(n.rank * kMaxRsplit + rp) * stride_prev + (col - row0_of(own, cols, n.world));
+              if (tg) st_pair<true>(n.arena[own] + off_prev, (long long)slot, v, tag);
+              else stg_cg(n.arena[own] + off_prev + slot, v);
             }
           };
         };
         const double *h = act_of(n.rank, l, cur);
-        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, p.lr, p.alpha, red, make_sink);
-        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, p.lr, p.alpha, red, make_sink);
+        if (tg) {  // the input vector of layer l from the previous sweep: present, but stored as pairs
+          stage_act(xs, l, cur, tag - 1);
+          __syncthreads();
+          h = xs;
+        }
+        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, tg, p.lr, p.alpha, red, make_sink);
+        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, tg, p.lr, p.alpha, red, make_sink);
         trace(100 + l);
-        bar.sync_all(n, (int)blockIdx.x < (n.ld[l] / cb) * plan.rsplit);
+        sync_phase((int)blockIdx.x < (n.ld[l] / cb) * plan.rsplit);
         trace(200 + l);
       }
       // ---- bottom-up: layer 0 update fused with its forward, then the rest
-      stage_delta(n, 0, layer_plan(n, 1, grid).rsplit, act_of(n.rank, 1, cur), ds);
-      forward_layer(0, 0, cur ^ 1, upd);
+      stage_delta(n, 0, layer_plan(n, 1, grid).rsplit, act_of(n.rank, 1, cur), ds, tg, tag);
+      forward_layer(0, 0, cur ^ 1, upd, tag);
       trace(300);
-      bar.sync_all(n, (int)blockIdx.x < n.rows[0]);
+      sync_phase((int)blockIdx.x < n.rows[0]);
       trace(400);
       for (int l = 1; l < NL; ++l) {
-        forward_layer(l, cur ^ 1, cur ^ 1, 0);
+        forward_layer(l, cur ^ 1, cur ^ 1, 0, tag);
         trace(300 + l);
-        bar.sync_all(n, (int)blockIdx.x < n.rows[l]);
+        sync_phase((int)blockIdx.x < n.rows[l]);
         trace(400 + l);
       }
       cur ^= 1;
       // ---- evaluate (every CTA, identical arithmetic => identical decision)
-      st = output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, n.row0[last], n.rows[last],
-                        ds, nullptr, red);
+      st = evaluate(tag, n.row0[last], n.rows[last], ds, nullptr);
       trace(2);
       dE = E - st.err;
       E = st.err;
@@ -166,10 +222,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
       if (!(dE > p.thr || !ok)) break;
     }
     // publish the final (normalised) output vector
-    if (blockIdx.x == 0)
-      output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, 0, 0, nullptr, A + n.off_out, red);
+    if (blockIdx.x == 0) evaluate(tag_of(iter), 0, 0, nullptr, A + n.off_out);
   }
   bar.finish();
+  if (blockIdx.x == 0 && threadIdx.x == 0) n.local_sync[160] = (unsigned)launch;
   if (blockIdx.x == 0 && threadIdx.x == 0 && p.result) {
     hpnn_train_result r;
     r.init_err = init_err;
@@ -243,11 +299,11 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
   }
   for (int i = 0; i <= NL; ++i) {
     net->off_act[i] = off;
-    off += pad(net->dims[i]) * (i == 0 ? 1 : 2);
+    off += pad(net->dims[i]) * (i == 0 ? 1 : 4);  // two buffers; each may hold {value, tag} pairs
   }
   for (int l = 0; l < NL; ++l) {
     net->off_part[l] = off;
-    off += (long long)W * kMaxRsplit * net->part_stride[l];  // slot (rank, row part)
+    off += 2LL * W * kMaxRsplit * net->part_stride[l];  // slot (rank, row part), {value, tag} pairs
   }
   net->off_target = off;
   off += pad(net->dims[NL]);
@@ -291,6 +347,18 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   p.min_iter = o->min_iter >= 0 ? o->min_iter : d.min_iter;
   p.max_iter = o->max_iter >= 0 ? o->max_iter : d.max_iter;
   p.result = result_dev;
+  {
+    // tagged hand-over wins when the phases are short (latency bound: 2x on SNN 784-1000-1000-10
+    // at 4 GPUs); with long bandwidth-bound phases the fence + flag barrier is cheaper than
+    // polling every vector (measured -7% on 8192-wide layers), so pick by local weight volume
+    const char *proto = getenv("HPNN_TP_PROTOCOL");
+    long long local_doubles = 0;
+    for (int l = 0; l < net->n_layers; ++l) local_doubles += (long long)net->rows[l] * net->ld[l];
+    bool tagged = net->world > 1 && local_doubles * 8 < (48LL << 20);
+    if (proto && !strcmp(proto, "barrier")) tagged = false;
+    if (proto && !strcmp(proto, "tagged")) tagged = net->world > 1;
+    p.tagged = tagged ? 1 : 0;
+  }
   p.trace = g_trace;
   p.trace_cap = g_trace_cap;
   int max_ld = 8, max_rows = 8;
@@ -323,13 +391,14 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
     set_error_msg("hpnn_dev_train_sample: layer too wide for the persistent kernel (use the multi-launch path)");
     return -2;
   }
-  cudaError_t e = cudaFuncSetAttribute(k_train_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const void *kfn = p.tagged ? (const void *)k_train_sample<true> : (const void *)k_train_sample<false>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) {
     set_error("cudaFuncSetAttribute(k_train_sample)", e);
     return -1;
   }
   void *args[] = {(void *)&p};
-  e = cudaLaunchCooperativeKernel((const void *)k_train_sample, dim3(grid), dim3(kThreads), args, smem,
+  e = cudaLaunchCooperativeKernel(kfn, dim3(grid), dim3(kThreads), args, smem,
                                   (cudaStream_t)stream);
   if (e != cudaSuccess) {
     set_error("cudaLaunchCooperativeKernel(k_train_sample)", e);

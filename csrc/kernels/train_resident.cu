@@ -45,90 +45,6 @@ __device__ __host__ inline int rp_count(int b, int shift, int grid, int rows) {
   return f < rows ? (rows - f + grid - 1) / grid : 0;
 }
 
-// ---- barrier-free hand-over: every value another CTA waits for travels as a 16-byte
-// {value, tag} pair written with ONE 128-bit store; the consumer spins on the pair itself until
-// the tag is the one it expects.  Data and "ready" flag arrive in the same access, so a phase
-// boundary costs one L2 write + one L2 read instead of a grid barrier plus a staging pass
-// (measured: a barrier is ~2600 cycles on B200, an L2 round trip ~800).  The tag is
-// (launch id << 32 | iteration): unique per buffer write, never equal to stale contents.
-__device__ __forceinline__ void st_pair(double *base, int idx, double v, unsigned long long tag) {
-  asm volatile("st.relaxed.gpu.global.v2.b64 [%0], {%1, %2};" ::"l"(base + 2 * (size_t)idx),
-               "l"(__double_as_longlong(v)), "l"(tag)
-               : "memory");
-}
-__device__ __forceinline__ bool ld_pair(const double *base, int idx, unsigned long long tag, double &v) {
-  long long a;
-  unsigned long long t;
-  asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(t) : "l"(base + 2 * (size_t)idx) : "memory");
-  v = __longlong_as_double(a);
-  return t == tag;
-}
-__device__ __forceinline__ double ld_pair_wait(const double *base, int idx, unsigned long long tag) {
-  double v;
-  while (!ld_pair(base, idx, tag, v)) {
-  }
-  return v;
-}
-// U tagged loads in flight per thread: all pending loads are issued back to back, then checked;
-// only the ones whose tag is still old are re-issued (one L2 round trip instead of U).
-#ifndef HPNN_POLL_BACKOFF_NS
-#define HPNN_POLL_BACKOFF_NS 0  /* measured: any back-off only adds latency (20.1 -> 24.2 us/iteration at 64 ns) */
-#endif
-constexpr unsigned kPollBackoffNs = HPNN_POLL_BACKOFF_NS;
-
-template <int U>
-__device__ __forceinline__ void ld_pairs_wait(const double *const (&addr)[U], const bool (&want)[U],
-                                              unsigned long long tag, double (&v)[U]) {
-  bool done[U];
-#pragma unroll
-  for (int u = 0; u < U; ++u) {
-    done[u] = !want[u];
-    v[u] = 0.0;
-  }
-  bool all;
-  do {
-    long long a[U];
-    unsigned long long t[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (!done[u])
-        asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(a[u]), "=l"(t[u]) : "l"(addr[u]) : "memory");
-    all = true;
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (!done[u]) {
-        if (t[u] == tag) {
-          v[u] = __longlong_as_double(a[u]);
-          done[u] = true;
-        } else {
-          all = false;
-        }
-      }
-    if (kPollBackoffNs && !all) __nanosleep(kPollBackoffNs);
-  } while (!all);
-}
-// gather a whole tagged vector (n values, padded to npad with zeros) into shared memory
-__device__ __forceinline__ void stage_pairs(double *dst, const double *pairs, int n, int npad, unsigned long long tag) {
-  constexpr int U = 4;
-  for (int base = threadIdx.x; base < npad; base += U * blockDim.x) {
-    const double *addr[U];
-    bool want[U];
-    double v[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = base + u * blockDim.x;
-      want[u] = i < n;
-      addr[u] = pairs + 2 * (size_t)(want[u] ? i : 0);
-    }
-    ld_pairs_wait<U>(addr, want, tag, v);
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int i = base + u * blockDim.x;
-      if (i < npad) dst[i] = v[u];
-    }
-  }
-}
-
 template <int UPD>
 __device__ __forceinline__ double smem_row(double *wrow, double *mrow, const double *xs, int ld, double s, double alpha,
                                            int lane) {
@@ -258,7 +174,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
       for (int q = 0; q < parts; ++q) z += red[64 + i * parts + q];
       const double v = kind == 0 ? act_f(z) : z;
       hown[s_doff[l] + i] = v;
-      st_pair(y, s_first[l] + i * grid, v, tag);
+      st_pair<false>(y, s_first[l] + i * grid, v, tag);
     }
   };
   // full forward sweep with tag `tag`; layer 0 optionally fused with its update
@@ -267,14 +183,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
     trace(300);
     for (int l = 1; l < NL; ++l) {
       __syncthreads();  // xs is free again
-      stage_pairs(xs, act_pairs(l), n.dims[l], n.ld[l], tag);
+      stage_pairs<false>(xs, act_pairs(l), n.dims[l], n.ld[l], tag);
       __syncthreads();
       trace(400 + l);
       forward_layer(l, xs, tag, 0);
       trace(300 + l);
     }
     __syncthreads();
-    stage_pairs(zout, act_pairs(NL), n_out, pad8(n_out), tag);  // the gathered output vector
+    stage_pairs<false>(zout, act_pairs(NL), n_out, pad8(n_out), tag);  // the gathered output vector
     __syncthreads();
     trace(500);
   };
@@ -303,7 +219,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
         // h = input vector of layer l as produced by the previous forward sweep (tag iter-1).
         // EVERY thread's h must be in before this CTA publishes a single partial: a fast
         // consumer may otherwise start the next forward sweep and overwrite act[l] under us.
-        stage_pairs(xs, act_pairs(l), n.dims[l], n.ld[l], tag - 1);
+        stage_pairs<false>(xs, act_pairs(l), n.dims[l], n.ld[l], tag - 1);
         __syncthreads();
         const double2 *h2 = reinterpret_cast<const double2 *>(xs);
         double *slot = A + n.off_cta_part[l] + (size_t)b * 2 * n.ld[l];
@@ -334,8 +250,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
               *mp = m;
             }
           }
-          st_pair(slot, 2 * c, acc.x, tag);
-          st_pair(slot, 2 * c + 1, acc.y, tag);
+          st_pair<false>(slot, 2 * c, acc.x, tag);
+          st_pair<false>(slot, 2 * c + 1, acc.y, tag);
         }
         trace(100 + l);
         // deltas of the rows this CTA owns in layer l-1: ordered sum over the CTA slots
@@ -353,7 +269,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
               want[u] = q < grid;
               addr[u] = part + ((size_t)(want[u] ? q : 0) * n.ld[l] + r) * 2;
             }
-            ld_pairs_wait<6>(addr, want, tag, v);
+            ld_pairs_wait<6, false>(addr, want, tag, v);
 #pragma unroll
             for (int u = 0; u < 6; ++u) s += v[u];
           }
