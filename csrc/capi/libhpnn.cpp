@@ -561,6 +561,12 @@ BOOL nn_train_kernel(nn_def *c) {
   // host momentum arrays are only needed by the CPU engine (the device kernel owns its own)
   const bool host_momentum = c->train == NN_TRAIN_BPM && !use_device();
   if (host_momentum) ann_momentum_init(k);
+  else if (c->train == NN_TRAIN_BPM) {
+    unsigned long bytes = 0;
+    for (UINT l = 0; l < k->n_hiddens; ++l) bytes += sizeof(double) * (unsigned long)((k->hiddens[l].n_inputs + 7) & ~7u) * k->hiddens[l].n_neurons;
+    bytes += sizeof(double) * (unsigned long)((k->output.n_inputs + 7) & ~7u) * k->output.n_neurons;
+    NN_OUT(stdout, "[GPU] MOMENTUM ALLOC: %lu (bytes)\n", bytes);
+  }
   std::vector<std::string> files = listed_files(c->samples);
   DIR *probe = opendir(c->samples);
   if (!probe) {
@@ -595,6 +601,41 @@ BOOL nn_train_kernel(nn_def *c) {
   return TRUE;
 }
 
+// verdict lines of nn_run_kernel for one sample (src/libhpnn.c:1443-1514)
+static void report_test(nn_def *c, const kernel_ann *k, const DOUBLE *o, const DOUBLE *t) {
+  if (c->type == NN_TYPE_SNN) {
+    DOUBLE res = 0.;
+    UINT guess = 0, want = 0;
+    NN_DBG(stdout, " CLASS | PROBABILITY (%%)\n");
+    NN_DBG(stdout, "-------|----------------\n");
+    for (UINT i = 0; i < k->n_outputs; ++i) {
+      NN_DBG(stdout, " %5i | %15.10f\n", i + 1, o[i] * 100.);
+      if (o[i] > res) {
+        res = o[i];
+        guess = i;
+      }
+      if (t[i] > 0.1) want = i;
+    }
+    NN_DBG(stdout, "-------|----------------\n");
+    NN_COUT(stdout, " BEST CLASS idx=%i P=%15.10f", guess + 1, res * 100);
+    if (guess == want) NN_COUT(stdout, " [PASS]\n");
+    else NN_COUT(stdout, " [FAIL idx=%i]\n", want + 1);
+  } else {
+    DOUBLE res = -1.;
+    UINT guess = k->n_outputs, want = TRUE;  // `is_ok=TRUE` start value of the reference
+    for (UINT i = 0; i < k->n_outputs; ++i) {
+      if (res < o[i]) {
+        guess = i;
+        res = o[i];
+      }
+      if (t[i] > 0.5) want = i;
+    }
+    if (guess == want) NN_COUT(stdout, " [PASS]\n");
+    else NN_COUT(stdout, " [FAIL idx=%i]\n", want + 1);
+  }
+  fflush(stdout);
+}
+
 void nn_run_kernel(nn_def *c) {
   if (!c || !c->kernel || !c->tests || !ann_like(c)) return;
   kernel_ann *k = (kernel_ann *)c->kernel;
@@ -608,6 +649,39 @@ void nn_run_kernel(nn_def *c) {
   if (c->seed == 0) c->seed = (UINT)time(NULL);
   std::vector<int> order(files.size());
   hpnn_shuffle_order(c->seed, (int)files.size(), order.data());
+  const int type = c->type == NN_TYPE_SNN ? HPNN_TYPE_SNN : HPNN_TYPE_ANN;
+  Shim *s = as_shim(k);
+  // Fast path (same verdicts, far fewer host round trips): parse every file in parallel, push the
+  // whole directory through the batched FP64 forward.  HPNN_RUN_BATCH=0 restores one launch per file.
+  const char *rb = getenv("HPNN_RUN_BATCH");
+  const int batch = rb ? atoi(rb) : 1024;
+  hpnn_net *dev = (batch > 0 && !files.empty()) ? device_for(s, type, s->dev_momentum) : nullptr;
+  if (dev && hpnn_net_world(dev) == 1) {
+    const int n_in = (int)k->n_inputs, n_out = (int)k->n_outputs, nf = (int)files.size();
+    std::vector<std::string> paths(nf);
+    std::vector<const char *> cpaths(nf);
+    for (int j = 0; j < nf; ++j) {
+      paths[j] = std::string(c->tests) + "/" + files[order[j]];
+      cpaths[j] = paths[j].c_str();
+    }
+    std::vector<double> X((size_t)nf * n_in), T((size_t)nf * n_out), Y((size_t)nf * n_out);
+    std::vector<unsigned char> ok(nf);
+    hpnn_sample_read_many(cpaths.data(), nf, n_in, n_out, X.data(), T.data(), ok.data());
+    bool fine = true;
+    for (int b0 = 0; b0 < nf && fine; b0 += batch) {
+      const int nb = nf - b0 < batch ? nf - b0 : batch;
+      fine = hpnn_net_forward_batch(dev, X.data() + (size_t)b0 * n_in, nb, Y.data() + (size_t)b0 * n_out, 0) == 0;
+    }
+    if (fine) {
+      for (int j = 0; j < nf; ++j) {
+        NN_OUT(stdout, "TESTING FILE: %16.16s\t", files[order[j]].c_str());
+        if (!ok[j]) continue;  // unreadable sample: skipped silently, as in the reference
+        report_test(c, k, Y.data() + (size_t)j * n_out, T.data() + (size_t)j * n_out);
+      }
+      return;
+    }
+    NN_WARN(stderr, "batched run failed (%s): falling back to one sample per launch\n", hpnn_last_error());
+  }
   for (int idx : order) {
     const std::string &name = files[idx];
     NN_OUT(stdout, "TESTING FILE: %16.16s\t", name.c_str());
@@ -620,40 +694,9 @@ void nn_run_kernel(nn_def *c) {
       continue;
     }
     memcpy(k->in, in, sizeof(double) * k->n_inputs);
-    const DOUBLE *o = k->output.vec;
-    if (c->type == NN_TYPE_SNN) {
-      snn_kernel_run(k);
-      DOUBLE res = 0.;
-      UINT guess = 0, want = 0;
-      NN_DBG(stdout, " CLASS | PROBABILITY (%%)\n");
-      NN_DBG(stdout, "-------|----------------\n");
-      for (UINT i = 0; i < k->n_outputs; ++i) {
-        NN_DBG(stdout, " %5i | %15.10f\n", i + 1, o[i] * 100.);
-        if (o[i] > res) {
-          res = o[i];
-          guess = i;
-        }
-        if (t[i] > 0.1) want = i;
-      }
-      NN_DBG(stdout, "-------|----------------\n");
-      NN_COUT(stdout, " BEST CLASS idx=%i P=%15.10f", guess + 1, res * 100);
-      if (guess == want) NN_COUT(stdout, " [PASS]\n");
-      else NN_COUT(stdout, " [FAIL idx=%i]\n", want + 1);
-    } else {
-      ann_kernel_run(k);
-      DOUBLE res = -1.;
-      UINT guess = k->n_outputs, want = TRUE;  // `is_ok=TRUE` start value of the reference
-      for (UINT i = 0; i < k->n_outputs; ++i) {
-        if (res < o[i]) {
-          guess = i;
-          res = o[i];
-        }
-        if (t[i] > 0.5) want = i;
-      }
-      if (guess == want) NN_COUT(stdout, " [PASS]\n");
-      else NN_COUT(stdout, " [FAIL idx=%i]\n", want + 1);
-    }
-    fflush(stdout);
+    if (c->type == NN_TYPE_SNN) snn_kernel_run(k);
+    else ann_kernel_run(k);
+    report_test(c, k, k->output.vec, t);
     FREE(in);
     FREE(t);
   }
@@ -739,6 +782,10 @@ void ann_momentum_init(kernel_ann *kernel) {
   Shim *s = as_shim(kernel);
   hpnn_cpu_momentum_init(s->host);
   refresh_views(s);
+  unsigned long bytes = 0;
+  for (int l = 0; l < hpnn_kernel_n_layers(s->host); ++l)
+    bytes += sizeof(double) * (unsigned long)hpnn_kernel_dim(s->host, l) * hpnn_kernel_dim(s->host, l + 1);
+  NN_OUT(stdout, "[CPU] MOMENTUM ALLOC: %lu (bytes)\n", bytes);  // src/ann.c:1904-1907
 }
 void ann_raz_momentum(kernel_ann *kernel) {
   if (kernel) hpnn_cpu_momentum_zero(as_shim(kernel)->host);

@@ -35,6 +35,9 @@ struct hpnn_net {
   double *pin = nullptr;  // pinned staging: input | target | output
   hpnn_train_result *pin_res = nullptr;
   size_t bytes_dev = 0;
+  // batched inference work space (grown on demand): two ping-pong activation matrices
+  double *bx = nullptr, *by = nullptr;
+  size_t bcap = 0;  // doubles per matrix
 };
 
 #define NET_CHECK(call, what)          \
@@ -62,6 +65,8 @@ void hpnn_net_destroy(hpnn_net *n) {
   }
   if (n->pin) cudaFreeHost(n->pin);
   if (n->pin_res) cudaFreeHost(n->pin_res);
+  if (n->bx) cudaFree(n->bx);
+  if (n->by) cudaFree(n->by);
   if (!n->ranks.empty()) cudaSetDevice(n->ranks[0].dev);
   delete n;
 }
@@ -229,6 +234,55 @@ int hpnn_net_train_sample(hpnn_net *n, const hpnn_train_opts *o, const double *i
   if (res) *res = *n->pin_res;
   const int NL = (int)n->dims.size() - 1;
   if (out) memcpy(out, n->pin + n->dims[0] + n->dims[NL], sizeof(double) * n->dims[NL]);
+  return 0;
+}
+
+// Batched forward of `batch` samples (row-major X [batch x n_in] on the host) through the FP64
+// DMMA GEMM path; Y [batch x n_out] on the host.  Single-GPU nets only (a row-split net is
+// served sample by sample through hpnn_net_run).  Extension: the reference is batch 1.
+int hpnn_net_forward_batch(hpnn_net *n, const double *X, int batch, double *Y, int stable_softmax) {
+  if (!n || !X || !Y || batch < 1) return -1;
+  if (n->world != 1) {
+    hpnn::set_error_msg("hpnn_net_forward_batch: single-GPU nets only");
+    return -2;
+  }
+  const int NL = (int)n->dims.size() - 1;
+  auto &r = n->ranks[0];
+  cudaSetDevice(r.dev);
+  int wmax = 0;
+  for (int d : n->dims) wmax = d > wmax ? d : wmax;
+  wmax = (wmax + 7) & ~7;
+  const size_t need = (size_t)batch * wmax;
+  if (need > n->bcap) {
+    if (n->bx) cudaFree(n->bx);
+    if (n->by) cudaFree(n->by);
+    n->bx = (double *)hpnn_dev_alloc(sizeof(double) * need);
+    n->by = (double *)hpnn_dev_alloc(sizeof(double) * need);
+    n->bcap = (n->bx && n->by) ? need : 0;
+    if (!n->bcap) return -1;
+  }
+  const int ld0 = (n->dims[0] + 7) & ~7;
+  NET_CHECK(cudaMemsetAsync(n->bx, 0, sizeof(double) * (size_t)batch * ld0, r.stream), "batch memset");
+  NET_CHECK(cudaMemcpy2DAsync(n->bx, sizeof(double) * ld0, X, sizeof(double) * n->dims[0], sizeof(double) * n->dims[0],
+                              batch, cudaMemcpyHostToDevice, r.stream),
+            "batch H2D");
+  double *cur = n->bx, *nxt = n->by;
+  int ldc = ld0;
+  for (int l = 0; l < NL; ++l) {
+    const int rows = n->dims[l + 1], ldn = (rows + 7) & ~7;
+    const int kind = (l == NL - 1 && n->type == HPNN_TYPE_SNN) ? 1 : 0;
+    if (hpnn_dev_forward_batch_f64(r.W[l], r.net.ld[l], rows, n->dims[l], cur, ldc, batch, nxt, ldn, kind, r.stream) != 0)
+      return -1;
+    double *t = cur;
+    cur = nxt;
+    nxt = t;
+    ldc = ldn;
+  }
+  if (n->type == HPNN_TYPE_SNN && hpnn_dev_softmax_rows(cur, ldc, batch, n->dims[NL], stable_softmax, r.stream) != 0) return -1;
+  NET_CHECK(cudaMemcpy2DAsync(Y, sizeof(double) * n->dims[NL], cur, sizeof(double) * ldc, sizeof(double) * n->dims[NL], batch,
+                              cudaMemcpyDeviceToHost, r.stream),
+            "batch D2H");
+  NET_CHECK(cudaStreamSynchronize(r.stream), "batch sync");
   return 0;
 }
 

@@ -44,8 +44,12 @@ def broadcast_kernel(kernel: Optional[Kernel], src: int = 0, group=None) -> Kern
     """Rank ``src`` reads / generates the kernel, everybody else receives it."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return kernel
+    # the reference sends a "bailout" int so that the other ranks do not hang when rank 0 cannot
+    # read the kernel (src/ann.c:242-245,551-555); here a None broadcast plays that role
     box = [kernel if dist.get_rank(group) == src else None]
     dist.broadcast_object_list(box, src=src, group=group)
+    if box[0] is None:
+        raise IOError("rank %d could not provide the kernel (bailout)" % src)
     return box[0]
 
 

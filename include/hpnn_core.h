@@ -268,6 +268,8 @@ int hpnn_net_download(hpnn_net *n, hpnn_kernel *k);       /* device weights -> h
 int hpnn_net_train_sample(hpnn_net *n, const hpnn_train_opts *o, const double *in, const double *target,
                           hpnn_train_result *res, double *out);
 int hpnn_net_run(hpnn_net *n, const double *in, double *out, int stable_softmax);
+/* batched forward, host matrices X [batch x n_in] -> Y [batch x n_out] (single-GPU nets; FP64 DMMA path) */
+int hpnn_net_forward_batch(hpnn_net *n, const double *X, int batch, double *Y, int stable_softmax);
 
 /* Forward pass for callers that must not allocate device memory.
  * (No counterpart in the reference: its CUDA path calls cudaMalloc per sample and per
