@@ -53,7 +53,7 @@ def main():
     for (a_, b_), v in seg.items():
         m = float(np.mean(v))
         tot += m
-        print(f"  {a_:4d} -> {b_:4d}: {m:9.0f} cycles")
+        print(f"  {a_:4d} -> {b_:4d}: {m:9.0f} cycles   (min {min(v)}, max {max(v)})")
     print(f"  total {tot:9.0f} cycles/iteration (SM clock)")
     eng.close()
 

@@ -7,6 +7,9 @@
 namespace hpnn {
 
 constexpr int kMaxRsplit = 4;  // row parts of a column task (see phase_cols)
+constexpr int kLazyChunk = 8;  // update factors kept per row / column by the deferred-update trainer
+constexpr int kLazyDotSlots = 160;  // per-CTA partial dot product slots per rank (>= grid size)
+constexpr long long kLazyMinBytes = 64LL << 20;  // local weights of layers >= 1 below this: not worth it
 
 struct KP {
   hpnn_dev_net net;
@@ -15,6 +18,7 @@ struct KP {
   int min_iter, max_iter;
   int max_ld, max_rows;  // shared-memory carve-up (doubles)
   int tagged;            // several ranks: tagged-pair hand-over instead of fence + flag barriers
+  int lazy_depth;        // deferred-update trainer: weights are written back every lazy_depth iterations
   hpnn_train_result *result;
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
@@ -197,5 +201,76 @@ __device__ __forceinline__ int owner_of_row(int row, int n, int world) {
   return (int)(((long long)(row + 1) * world - 1) / n);
 }
 __device__ __forceinline__ int row0_of(int g, int n, int world) { return (int)((long long)g * n / world); }
+
+// delta_l[r] = dact(h_l[r]) * sum_g part_l[g][r] for the owned rows, into shared memory
+// column-task plan of layer l; computed from the LARGEST row slice so that every rank agrees
+__device__ __forceinline__ ColPlan layer_plan(const hpnn_dev_net &n, int l, int grid) {
+  return pick_col_plan(n.ld[l], (n.dims[l + 1] + n.world - 1) / n.world, grid, kMaxRsplit);
+}
+
+// (rank g, row part rp of the producing layer) lives in slot g*kMaxRsplit + rp
+// tagged: partials and activations are {value, tag} pairs; the partials are polled until `tag`
+__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, int rsplit, const double *act_next, double *ds,
+                                            bool tagged, unsigned long long tag) {
+  const double *part = n.arena[n.rank] + n.off_part[l];
+  const int stride = n.part_stride[l];
+  const int combos = n.world * rsplit;  // (rank, row part) slots, summed rank-major
+  if (!tagged) {
+    // four rows per thread and round, every load of a round issued before the first use: the
+    // staging pass costs ~rows/2048 L2 round trips instead of one per row and slot
+    constexpr int U = 4;
+    const int rows = n.rows[l];
+    for (int r0 = threadIdx.x; r0 < rows; r0 += U * blockDim.x) {
+      double s[U], hn[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int r = r0 + u * blockDim.x;
+        s[u] = 0.0;
+        hn[u] = (r < rows) ? ldg_cg(act_next + n.row0[l] + r) : 0.0;
+      }
+      for (int g = 0; g < n.world; ++g)
+        for (int rp = 0; rp < rsplit; ++rp) {
+          const double *src = part + (size_t)(g * kMaxRsplit + rp) * stride;
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int r = r0 + u * blockDim.x;
+            if (r < rows) s[u] += ldg_cg(src + r);
+          }
+        }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int r = r0 + u * blockDim.x;
+        if (r < rows) ds[r] = s[u] * dact_f(hn[u]);
+      }
+    }
+    return;
+  }
+  for (int r = threadIdx.x; r < n.rows[l]; r += blockDim.x) {
+    double s = 0.0;
+    if (tagged) {
+      for (int c0 = 0; c0 < combos; c0 += 8) {  // 8 polls in flight
+        const double *addr[8];
+        bool want[8];
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = c0 + u;
+          want[u] = c < combos;
+          const int g = want[u] ? c / rsplit : 0, rp = want[u] ? c % rsplit : 0;
+          addr[u] = part + 2 * ((size_t)(g * kMaxRsplit + rp) * stride + r);
+        }
+        ld_pairs_wait<8, false>(addr, want, tag, v);  // local arena: GPU-scope loads see the peers' stores
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s += v[u];
+      }
+    } else {
+      for (int g = 0; g < n.world; ++g)
+        for (int rp = 0; rp < rsplit; ++rp) s += ldg_cg(part + (size_t)(g * kMaxRsplit + rp) * stride + r);
+    }
+    const size_t hidx = (size_t)(n.row0[l] + r) * (tagged ? 2 : 1);  // own output of the previous sweep
+    ds[r] = s * dact_f(ldg_cg(act_next + hidx));
+  }
+}
+
 
 }  // namespace hpnn

@@ -99,6 +99,11 @@ extern "C" int hpnn_dev_forward_noalloc(int type, int stable_softmax, int n_laye
     net.cta_slots = 0;
     net.arena_doubles = need;
   }
+  if (need > 0 && net.hist_depth > 0) {  // training-only region behind everything a forward pass uses
+    if (net.off_hist_u[1] < need) need = net.off_hist_u[1];
+    net.hist_depth = 0;
+    net.arena_doubles = need;
+  }
   if (need <= 0 || need > (long long)HPNN_NOALLOC_MAX_DOUBLES) {
     char msg[256];
     snprintf(msg, sizeof(msg),

@@ -23,46 +23,6 @@
 
 namespace hpnn {
 
-// delta_l[r] = dact(h_l[r]) * sum_g part_l[g][r] for the owned rows, into shared memory
-// column-task plan of layer l; computed from the LARGEST row slice so that every rank agrees
-__device__ __forceinline__ ColPlan layer_plan(const hpnn_dev_net &n, int l, int grid) {
-  return pick_col_plan(n.ld[l], (n.dims[l + 1] + n.world - 1) / n.world, grid, kMaxRsplit);
-}
-
-// (rank g, row part rp of the producing layer) lives in slot g*kMaxRsplit + rp
-// tagged: partials and activations are {value, tag} pairs; the partials are polled until `tag`
-__device__ __forceinline__ void stage_delta(const hpnn_dev_net &n, int l, int rsplit, const double *act_next, double *ds,
-                                            bool tagged, unsigned long long tag) {
-  const double *part = n.arena[n.rank] + n.off_part[l];
-  const int stride = n.part_stride[l];
-  const int combos = n.world * rsplit;  // (rank, row part) slots, summed rank-major
-  for (int r = threadIdx.x; r < n.rows[l]; r += blockDim.x) {
-    double s = 0.0;
-    if (tagged) {
-      for (int c0 = 0; c0 < combos; c0 += 8) {  // 8 polls in flight
-        const double *addr[8];
-        bool want[8];
-        double v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int c = c0 + u;
-          want[u] = c < combos;
-          const int g = want[u] ? c / rsplit : 0, rp = want[u] ? c % rsplit : 0;
-          addr[u] = part + 2 * ((size_t)(g * kMaxRsplit + rp) * stride + r);
-        }
-        ld_pairs_wait<8, false>(addr, want, tag, v);  // local arena: GPU-scope loads see the peers' stores
-#pragma unroll
-        for (int u = 0; u < 8; ++u) s += v[u];
-      }
-    } else {
-      for (int g = 0; g < n.world; ++g)
-        for (int rp = 0; rp < rsplit; ++rp) s += ldg_cg(part + (size_t)(g * kMaxRsplit + rp) * stride + r);
-    }
-    const size_t hidx = (size_t)(n.row0[l] + r) * (tagged ? 2 : 1);  // own output of the previous sweep
-    ds[r] = s * dact_f(ldg_cg(act_next + hidx));
-  }
-}
-
 // TG: tagged-pair hand-over between ranks (world > 1); false = plain buffers + barriers
 template <bool TG>
 __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_constant__ KP p) {
@@ -241,6 +201,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
 
 // defined in train_resident.cu: 0 = launched, < 0 = error, 1 = not eligible (use the streaming kernel)
 int launch_resident_if_eligible(const KP &p, int grid, void *stream);
+// defined in train_lazy.cu, same convention
+int launch_lazy_if_eligible(const KP &p, int grid, size_t smem, void *stream);
+extern long long g_lazy_min_bytes;
 
 // ------------------------------- host side ---------------------------------
 static int g_grid_override = 0;
@@ -326,6 +289,25 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
       }
     }
   }
+  // update-factor history of the deferred-update trainer: only where the weights of the layers
+  // l >= 1 are far larger than L2, i.e. where a saved pass over W is worth the bookkeeping
+  net->hist_depth = 0;
+  for (int l = 0; l < NL; ++l) net->off_hist_u[l] = net->off_hist_v[l] = net->off_hist_dot[l] = 0;
+  {
+    long long wbytes = 0;
+    for (int l = 1; l < NL; ++l) wbytes += 8LL * net->part_stride[l] * net->ld[l];
+    if (wbytes >= (g_lazy_min_bytes >= 0 ? g_lazy_min_bytes : kLazyMinBytes)) {
+      net->hist_depth = kLazyChunk;
+      for (int l = 1; l < NL; ++l) {
+        net->off_hist_u[l] = off;
+        off += (long long)kLazyChunk * net->part_stride[l];
+        net->off_hist_v[l] = off;
+        off += (long long)kLazyChunk * net->ld[l];
+        net->off_hist_dot[l] = off;
+        off += (long long)kLazyChunk * W * kLazyDotSlots;
+      }
+    }
+  }
   net->arena_doubles = off;
   return off;
 }
@@ -359,6 +341,7 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
     if (proto && !strcmp(proto, "tagged")) tagged = net->world > 1;
     p.tagged = tagged ? 1 : 0;
   }
+  p.lazy_depth = 0;
   p.trace = g_trace;
   p.trace_cap = g_trace_cap;
   int max_ld = 8, max_rows = 8;
@@ -373,6 +356,20 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   p.max_ld = max_ld;
   p.max_rows = (max_rows + 7) & ~7;
   const int grid = hpnn_dev_persistent_grid();
+  int rowpart = 8;
+  for (int l = 0; l < net->n_layers; ++l) {
+    const int d = row_part_doubles(net->rows[l], grid);
+    rowpart = d > rowpart ? d : rowpart;
+  }
+  const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles + rowpart);
+  if (smem <= 227 * 1024) {
+    // BP on layers far larger than L2: deferred rank-1 updates save most of the write-back traffic
+    const int rc = launch_lazy_if_eligible(p, grid, smem, stream);
+    if (rc <= 0) {
+      if (rc == 0) ++g_launches;
+      return rc;
+    }
+  }
   {
     // small nets: keep every weight (and momentum) row in shared memory for the whole sample
     const int rc = launch_resident_if_eligible(p, grid, stream);
@@ -381,12 +378,6 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
       return rc;
     }
   }
-  int rowpart = 8;
-  for (int l = 0; l < net->n_layers; ++l) {
-    const int d = row_part_doubles(net->rows[l], grid);
-    rowpart = d > rowpart ? d : rowpart;
-  }
-  const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles + rowpart);
   if (smem > 227 * 1024) {
     set_error_msg("hpnn_dev_train_sample: layer too wide for the persistent kernel (use the multi-launch path)");
     return -2;

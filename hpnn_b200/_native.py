@@ -43,7 +43,10 @@ class DevNet(C.Structure):
                 ("off_act", C.c_longlong * (MAX_LAYERS + 1)), ("off_part", C.c_longlong * MAX_LAYERS),
                 ("off_target", C.c_longlong), ("off_out", C.c_longlong), ("off_flags", C.c_longlong),
                 ("arena_doubles", C.c_longlong), ("part_stride", C.c_int * MAX_LAYERS),
-                ("off_cta_part", C.c_longlong * MAX_LAYERS), ("cta_slots", C.c_int)]
+                ("off_cta_part", C.c_longlong * MAX_LAYERS), ("cta_slots", C.c_int),
+                ("off_hist_u", C.c_longlong * MAX_LAYERS), ("off_hist_v", C.c_longlong * MAX_LAYERS),
+                ("off_hist_dot", C.c_longlong * MAX_LAYERS),
+                ("hist_depth", C.c_int)]
 
 
 _lib = None
@@ -101,6 +104,7 @@ def _declare(lib):
         "hpnn_dev_train_sample": (i, [C.POINTER(DevNet), C.POINTER(TrainOpts), i, vp, vp]),
         "hpnn_dev_persistent_grid": (i, []),
         "hpnn_dev_set_persistent_grid": (None, [i]),
+        "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),
         "hpnn_dev_set_phase_trace": (None, [vp, i]),
         "hpnn_dev_forward_layer": (i, [vp, i, i, i, vp, vp, i, vp]),
         "hpnn_dev_output_stats": (i, [i, i, vp, vp, i, vp, vp, vp, vp]),

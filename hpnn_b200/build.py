@@ -32,6 +32,7 @@ CORE_SOURCES = [
     "csrc/core/device_net.cu",
     "csrc/kernels/train_persistent.cu",
     "csrc/kernels/train_resident.cu",
+    "csrc/kernels/train_lazy.cu",
     "csrc/kernels/ops.cu",
     "csrc/kernels/gemm_umma.cu",
     "csrc/kernels/noalloc.cu",

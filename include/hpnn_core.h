@@ -166,7 +166,21 @@ typedef struct {
    * cta_slots x ld[l] {value, tag} pairs for layer l >= 1 (0 slots = variant not available) */
   long long off_cta_part[HPNN_MAX_LAYERS];
   int cta_slots;
+  /* deferred rank-1 updates of the wide-layer BP trainer (train_lazy.cu): for layer l >= 1 the
+   * last hist_depth (<= 8) update factors, u = lr*delta per owned row and v = input per column,
+   * stored as 8-double chunks per row / column (0 = variant not available for this shape) */
+  long long off_hist_u[HPNN_MAX_LAYERS];
+  long long off_hist_v[HPNN_MAX_LAYERS];
+  /* per-(rank, CTA) partial dot products v_j . x of layer l >= 1, world x 160 chunks of 8 */
+  long long off_hist_dot[HPNN_MAX_LAYERS];
+  int hist_depth;
 } hpnn_dev_net;
+
+/* Deferred-update BP trainer for layers much larger than L2 (train_lazy.cu).  depth: write-back
+ * period, 2..8; 0 disables the variant; -1 restores the default (HPNN_LAZY / HPNN_LAZY_DEPTH).
+ * min_bytes: smallest local weight volume of the layers >= 1 for which hpnn_dev_arena_layout
+ * reserves the factor history (-1 = default 64 MiB); set it BEFORE laying out a network. */
+void hpnn_dev_set_lazy(int depth, long long min_bytes);
 
 /* fills ld/row0/rows/offsets from dims/rank/world; returns arena size in doubles */
 long long hpnn_dev_arena_layout(hpnn_dev_net *net);

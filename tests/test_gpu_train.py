@@ -103,3 +103,33 @@ def test_multi_launch_path_with_logical_ranks(world, nn_type, train):
     for wa, wb in zip(eng.kernel().weights, cpu.kernel().weights):
         np.testing.assert_allclose(wa, wb, atol=1e-12)
     np.testing.assert_allclose(eng.run(X[0]), cpu.run(X[0]), atol=1e-12)
+
+
+@pytest.mark.parametrize("depth", [2, 3, 8])
+@pytest.mark.parametrize("nn_type", [N.TYPE_ANN, N.TYPE_SNN])
+def test_deferred_update_trainer_matches_cpu_engine(depth, nn_type):
+    """K-PL (train_lazy.cu) keeps the rank-1 updates of the layers >= 1 in factored form and writes
+    them back every `depth` iterations; a fixed iteration count must reproduce the CPU engine's
+    weights to round-off, whatever the count is relative to the write-back period."""
+    lib = N.load()
+    lib.hpnn_dev_set_lazy(depth, 0)  # reserve the factor history for every shape
+    try:
+        k, _ = hp.generate_kernel(77, 40, [600, 300, 150], 12)
+        X, T = make_problem(nn_type, 40, (600, 300, 150), 12, n_samples=3, seed=3)
+        for n_it in (1, 7, 16, 37):
+            kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
+            gpu = CudaEngine(k, nn_type, N.TRAIN_BP, **kw)
+            assert gpu.net.net.hist_depth == 8
+            cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw)
+            for x, t in zip(X, T):
+                rg, rc = gpu.train(x, t), cpu.train(x, t)
+                assert rg.n_iter == rc.n_iter == n_it
+                assert abs(rg.init_err - rc.init_err) < 1e-12
+                assert abs(rg.last_err - rc.last_err) < 1e-11
+            for a, b in zip(gpu.kernel().weights, cpu.kernel().weights):
+                np.testing.assert_allclose(a, b, atol=1e-11)
+            np.testing.assert_allclose(gpu.run(X[0]), cpu.run(X[0]), atol=1e-10)
+            gpu.close()
+            cpu.close()
+    finally:
+        lib.hpnn_dev_set_lazy(-1, -1)
