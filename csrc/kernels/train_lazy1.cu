@@ -1,0 +1,445 @@
+// K-PL1: deferred-update BP trainer for ONE GPU, organised around row panels.
+//
+// Same arithmetic as train_lazy.cu (W_true = S + sum_j u_j (x) v_j, write-back every `depth`
+// iterations; src/ann.c:2281-2467 is the loop being reproduced), different work split: CTA b
+// owns one contiguous panel of rows of every layer for the whole sample, in every phase.
+//
+//   forward   : one warp per (row, segment) of the own panel, as in the other trainers.
+//   top-down  : the CTA streams its panel once, every thread owning a few column pairs:
+//               P_b[c] = sum_{r in panel} W[r,c] delta[r].  No cross-thread reduction, no CTA-wide
+//               barrier inside the pass, every row is read as one contiguous 32 KB run, so this
+//               pass runs at the forward pass's bandwidth (the column tasks of K-P / K-PL reach
+//               ~5.2 TB/s against ~6.3 TB/s because each task ends in a block-wide reduction).
+//               P_b goes to a per-CTA slot in global memory (148 x 64 KB, L2 resident).
+//   [barrier]
+//   reduce    : CTA b adds the 148 partial vectors for the columns that are ITS rows of the layer
+//               below and turns them into that layer's deltas.  Deltas and the u factors
+//               therefore never leave the CTA: they live in shared memory, the per-CTA staging of
+//               the full delta vector (8192 x 3 loads per CTA and layer) is gone, and the
+//               write-back pass reads its u factors as shared-memory broadcasts.
+//
+// The v factors (one 8-chunk per column), the partial dot products v_j . x and the partial
+// u_j . delta travel through global memory exactly as in train_lazy.cu.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "lazy_common.cuh"
+
+namespace hpnn {
+
+void set_error(const char *what, cudaError_t e);
+void set_error_msg(const char *what);
+int lazy_depth_setting();
+
+struct Panel {
+  int r0, cnt;
+};
+// contiguous balanced split of `rows` over the first min(grid, rows) CTAs
+__host__ __device__ inline Panel panel_of(int rows, int grid, int b) {
+  const int nb = grid < rows ? grid : rows;
+  Panel p;
+  if (b >= nb) {
+    p.r0 = rows;
+    p.cnt = 0;
+    return p;
+  }
+  p.r0 = (int)((long long)b * rows / nb);
+  p.cnt = (int)((long long)(b + 1) * rows / nb) - p.r0;
+  return p;
+}
+__host__ __device__ inline int panel_max(int rows, int grid) {
+  const int nb = grid < rows ? grid : rows;
+  return nb > 0 ? (rows + nb - 1) / nb : 0;
+}
+
+constexpr int kPanelCols = 2 * kThreads;  // columns covered by one pass of the CTA (one double2 per thread)
+
+// Read-only top-down pass over the own panel: four column chunks per thread, rows outermost, two
+// rows in flight.  Pout[c] = sum_i W[r0+i, c] * dsl[i].
+__device__ __forceinline__ void panel_cols_read(const double *W, int ld, Panel pn, const double *dsl, double *Pout) {
+  constexpr int G = 4;  // chunks per group
+  for (int g0 = 0; g0 < ld; g0 += G * kPanelCols) {
+    const int cbase = g0 + 2 * threadIdx.x;
+    double2 acc[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) acc[k] = make_double2(0.0, 0.0);
+    const double2 zero2 = make_double2(0.0, 0.0);
+    double2 wa[G], wb[G];
+    auto load = [&](double2 (&w)[G], int i) {
+      const double *row = W + (size_t)(pn.r0 + i) * ld;
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        const int c = cbase + k * kPanelCols;
+        w[k] = (i < pn.cnt && c < ld) ? ldg_cg2(reinterpret_cast<const double2 *>(row + c)) : zero2;
+      }
+    };
+    auto consume = [&](double2 (&w)[G], int i) {
+      if (i < pn.cnt) {
+        const double d = dsl[i];
+#pragma unroll
+        for (int k = 0; k < G; ++k) {
+          acc[k].x = fma(w[k].x, d, acc[k].x);
+          acc[k].y = fma(w[k].y, d, acc[k].y);
+        }
+      }
+    };
+    load(wa, 0);
+    for (int i = 0; i < pn.cnt; i += 2) {
+      load(wb, i + 1);
+      consume(wa, i);
+      load(wa, i + 2);
+      consume(wb, i + 1);
+    }
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      const int c = cbase + k * kPanelCols;
+      if (c < ld) stg_cg2(reinterpret_cast<double2 *>(Pout + c), acc[k]);
+    }
+  }
+}
+
+// Top-down pass that also brings S up to date (column chunk outermost: the 2 x 8 v factors of
+// the thread's column pair stay in registers for the whole panel):
+//   P[c] from the OLD stored weights, then w += sum_{j<m} us[i][j] v_j[c] + (lr*d_i) h[c].
+// Pout == nullptr: final write-back, no sums wanted.
+__device__ __forceinline__ void panel_cols_flush(double *W, int ld, Panel pn, const double *dsl, const double *us,
+                                                 const double *HV, const double *h, double lr, int m, double *Pout) {
+  const double2 zero2 = make_double2(0.0, 0.0);
+  const int mc = (m + 1) >> 1;
+  for (int c = 2 * threadIdx.x; c < ld; c += kPanelCols) {
+    const double h0 = ldg_cg(h + c), h1 = ldg_cg(h + c + 1);
+    double v0[kLazyChunk], v1[kLazyChunk];
+    {
+      const double2 *a = reinterpret_cast<const double2 *>(HV + (size_t)c * kLazyChunk);
+      const double2 *b = a + kLazyChunk / 2;
+#pragma unroll
+      for (int k = 0; k < kLazyChunk / 2; ++k) {
+        const bool on = 2 * k < m;
+        const double2 qa = on ? ldg_cg2(a + k) : zero2;
+        const double2 qb = on ? ldg_cg2(b + k) : zero2;
+        v0[2 * k] = qa.x;
+        v0[2 * k + 1] = (2 * k + 1 < m) ? qa.y : 0.0;
+        v1[2 * k] = qb.x;
+        v1[2 * k + 1] = (2 * k + 1 < m) ? qb.y : 0.0;
+      }
+    }
+    double a0 = 0.0, a1 = 0.0;
+    double2 *Wp = reinterpret_cast<double2 *>(W + (size_t)pn.r0 * ld + c);
+    const size_t stride2 = (size_t)(ld >> 1);
+    double2 wa[4], wb[4];
+    auto load = [&](double2 (&w)[4], int i0) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) w[u] = (i0 + u < pn.cnt) ? ldg_cg2(Wp + (size_t)(i0 + u) * stride2) : zero2;
+    };
+    auto consume = [&](double2 (&w)[4], int i0) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u;
+        if (i < pn.cnt) {
+          const double d = dsl[i];
+          a0 = fma(w[u].x, d, a0);
+          a1 = fma(w[u].y, d, a1);
+          const double2 *uc = reinterpret_cast<const double2 *>(us + (size_t)i * kLazyChunk);
+#pragma unroll
+          for (int k = 0; k < kLazyChunk / 2; ++k) {
+            if (k < mc) {
+              const double2 f = uc[k];  // same address in every thread: a shared-memory broadcast
+              w[u].x = fma(f.x, v0[2 * k], w[u].x);
+              w[u].y = fma(f.x, v1[2 * k], w[u].y);
+              if (2 * k + 1 < m) {
+                w[u].x = fma(f.y, v0[2 * k + 1], w[u].x);
+                w[u].y = fma(f.y, v1[2 * k + 1], w[u].y);
+              }
+            }
+          }
+          const double s = lr * d;
+          w[u].x = fma(s, h0, w[u].x);
+          w[u].y = fma(s, h1, w[u].y);
+          stg_cg2(Wp + (size_t)i * stride2, w[u]);
+        }
+      }
+    };
+    load(wa, 0);
+    for (int i0 = 0; i0 < pn.cnt; i0 += 8) {
+      load(wb, i0 + 4);
+      consume(wa, i0);
+      load(wa, i0 + 8);
+      consume(wb, i0 + 4);
+    }
+    if (Pout) stg_cg2(reinterpret_cast<double2 *>(Pout + c), make_double2(a0, a1));
+  }
+}
+
+// Row tasks over the own panel.
+//   UPD 0: z_i = S[r,:].x + sum_j us[i][j] coef[j]      (read-only; us == nullptr or m == 0: plain)
+//   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                (layer 0)
+// y goes to out[r]; while it is at hand the CTA's share of the next layer's v_j . y is formed.
+template <int UPD>
+__device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
+                                           int act_kind, double *out, int segs, double *rowpart, const double *us,
+                                           const double *coef, int m, const DotOut &dots, double *red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n2 = ld >> 1;
+  const int seg2 = (n2 + segs - 1) / segs;
+  for (int u = warp; u < pn.cnt * segs; u += kWarps) {
+    const int i = u / segs, sg = u % segs;
+    const int c0 = sg * seg2, c1 = min(n2, c0 + seg2);
+    double *wrow = W + (size_t)(pn.r0 + i) * ld + 2 * c0;
+    const double s = UPD ? lr * dsl[i] : 0.0;
+    const double z = c1 > c0 ? warp_row<UPD>(wrow, nullptr, xs + 2 * c0, 2 * (c1 - c0), s, 0.0, lane) : 0.0;
+    if (lane == 0) rowpart[i * 8 + sg] = z;
+  }
+  __syncthreads();
+  const bool want_dots = dots.p[0] != nullptr && m > 0 && pn.cnt > 0;
+  double acc[kLazyChunk];
+#pragma unroll
+  for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
+  for (int i = threadIdx.x; i < pn.cnt; i += blockDim.x) {
+    double z = 0.0;
+    for (int sg = 0; sg < segs; ++sg) z += rowpart[i * 8 + sg];
+    if (!UPD && us && m > 0) {
+      double corr = 0.0;
+      for (int j = 0; j < m; ++j) corr = fma(us[(size_t)i * kLazyChunk + j], coef[j], corr);
+      z += corr;
+    }
+    const double y = act_kind == 0 ? act_f(z) : z;
+    stg_cg(out + pn.r0 + i, y);
+    if (want_dots) chunk_fma(dots.HV + (size_t)(pn.r0 + i) * kLazyChunk, y, m, acc);
+  }
+  if (want_dots) {  // CTA-uniform
+    __shared__ double mine_dots[kLazyChunk];
+    chunk_block_sum(acc, m, mine_dots, red);
+    if (threadIdx.x < kLazyChunk) stg_cg(dots.p[0] + threadIdx.x, mine_dots[threadIdx.x]);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid_constant__ KP p) {
+  extern __shared__ double smem[];
+  const hpnn_dev_net &n = p.net;
+  const int NL = n.n_layers;
+  const int grid = gridDim.x, b = blockIdx.x;
+  const int pmax = p.max_rows;  // here: widest panel, padded to 8 (see the launcher)
+  double *xs = smem;                 // input vector of the running forward phase
+  double *dsl = xs + p.max_ld;       // deltas of the own panel of the layer being processed
+  double *us = dsl + pmax;           // u factors of the own panels: [layer][row][8]
+  double *red = us + (size_t)NL * pmax * kLazyChunk;
+  double *rowpart = red + kRedDoubles;
+  __shared__ double coef[kLazyChunk];
+
+  const int n_out = n.dims[NL];
+  double *A = n.arena[0];
+  const bool snn = p.type == HPNN_TYPE_SNN;
+  const int depth = p.lazy_depth;
+
+  Barrier bar;
+  bar.init(n);
+  int trace_n = 0;
+  auto trace = [&](int tag) {
+    if (p.trace && b == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
+      p.trace[2 * trace_n] = tag;
+      p.trace[2 * trace_n + 1] = clock64();
+      ++trace_n;
+    }
+  };
+  int cur = 0;
+  auto act_of = [&](int i, int buf) -> double * {
+    return A + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]));
+  };
+  auto panel = [&](int l) { return panel_of(n.dims[l + 1], grid, b); };
+  auto us_of = [&](int l) { return us + (size_t)l * pmax * kLazyChunk; };
+  // per-CTA slots: partial column sums (+ 8 partial u_j . delta behind them), two buffers
+  auto pslot = [&](int buf, int cta) { return A + n.off_panel + ((size_t)buf * kLazyDotSlots + cta) * n.panel_stride; };
+
+  auto forward = [&](int l, int src_buf, int dst_buf, int u, int m) {
+    stage_vec(xs, act_of(l, src_buf), pad8(n.dims[l]));
+    __syncthreads();
+    if (l >= 1 && m > 0) gather_dots(n, l, m, coef, red);  // coef[j] = v_j . x
+    DotOut dots;
+    dots.n = 1;
+    dots.p[0] = nullptr;
+    if (l + 1 < NL && m > 0) {
+      dots.p[0] = A + n.off_hist_dot[l + 1] + (size_t)b * kLazyChunk;
+      dots.HV = A + n.off_hist_v[l + 1];
+      dots.row0 = 0;
+    }
+    const int kind = (snn && l == NL - 1) ? 1 : 0;
+    const int segs = pick_row_segments(n.dims[l + 1], n.ld[l], grid);
+    if (u) panel_rows<1>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, act_of(l + 1, dst_buf), segs, rowpart, nullptr, coef, m, dots, red);
+    else panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, act_of(l + 1, dst_buf), segs, rowpart, l >= 1 ? us_of(l) : nullptr, coef, m, dots, red);
+  };
+
+  for (int l = 0; l < NL; ++l) {
+    forward(l, cur, cur, 0, 0);
+    bar.sync_local();
+  }
+  const double *target = A + n.off_target;
+  const int last = NL - 1;
+  const Panel plast = panel(last);
+  OutStats st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, plast.r0, plast.cnt, dsl, nullptr, red);
+  double E = st.err;
+  const double init_err = E;
+  int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
+  double dE = 0.0;
+  int m = 0;  // pending factors of every layer l >= 1 (identical on all CTAs)
+
+  for (;;) {
+    ++iter;
+    trace(1);
+    const bool flush = (m + 1 >= depth);
+    // ---- top-down
+    for (int l = last; l >= 1; --l) {
+      const Panel pn = panel(l);
+      double *ul = us_of(l);
+      double *HV = A + n.off_hist_v[l];
+      const double *h = act_of(l, cur);
+      double *Pout = pslot(l & 1, b);
+      if (pn.cnt > 0 && threadIdx.x < 32) {
+        // this panel's share of u_j . delta (factor j = lane & 7, rows dealt to the four lane groups),
+        // parked behind the column sums.  Reads slots < m only: no conflict with the append below.
+        const int j = threadIdx.x & 7;
+        double s = 0.0;
+        if (j < m)
+          for (int i = threadIdx.x >> 3; i < pn.cnt; i += 4) s = fma(ul[(size_t)i * kLazyChunk + j], dsl[i], s);
+        s += __shfl_xor_sync(0xffffffffu, s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 16);
+        if (threadIdx.x < kLazyChunk) stg_cg(Pout + n.panel_stride - kLazyChunk + j, s);
+      }
+      if (!flush) {
+        for (int i = threadIdx.x; i < pn.cnt; i += kThreads) ul[(size_t)i * kLazyChunk + m] = p.lr * dsl[i];
+        const int gt = b * kThreads + threadIdx.x;
+        for (int c = gt; c < n.ld[l]; c += grid * kThreads) stg_cg(HV + (size_t)c * kLazyChunk + m, ldg_cg(h + c));
+        if (pn.cnt > 0) panel_cols_read(n.W[l], n.ld[l], pn, dsl, Pout);
+      } else if (pn.cnt > 0) {
+        panel_cols_flush(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
+      }
+      trace(100 + l);
+      bar.sync_local();
+      trace(200 + l);
+      // ---- reduce: deltas of the own panel of layer l-1 from everybody's partial sums
+      const int nbp = grid < n.dims[l + 1] ? grid : n.dims[l + 1];  // CTAs that own rows of layer l
+      if (m > 0) {
+        double acc[kLazyChunk];
+#pragma unroll
+        for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
+        for (int q = threadIdx.x; q < nbp; q += kThreads)
+          chunk_fma(pslot(l & 1, q) + n.panel_stride - kLazyChunk, 1.0, m, acc);
+        chunk_block_sum(acc, m, coef, red);  // coef[j] = u_j . delta_l
+      }
+      const Panel below = panel(l - 1);
+      const double *hb = act_of(l, cur);  // output of layer l-1
+      for (int ci0 = 0; ci0 < below.cnt; ci0 += 64) {
+        const int ci = ci0 + (threadIdx.x & 63), g = threadIdx.x >> 6;
+        double s = 0.0;
+        if (ci < below.cnt)
+          for (int q = g; q < nbp; q += kThreads / 64) s += ldg_cg(pslot(l & 1, q) + below.r0 + ci);
+        __syncthreads();
+        red[threadIdx.x] = s;
+        __syncthreads();
+        if (threadIdx.x < 64 && ci < below.cnt) {
+          double pc = 0.0;
+#pragma unroll
+          for (int gg = 0; gg < kThreads / 64; ++gg) pc += red[gg * 64 + threadIdx.x];
+          const int c = below.r0 + ci;
+          if (m > 0) pc += chunk_apply(HV + (size_t)c * kLazyChunk, coef, m);
+          dsl[ci] = pc * dact_f(ldg_cg(hb + c));
+        }
+      }
+      __syncthreads();
+    }
+    m = flush ? 0 : m + 1;
+    // ---- bottom-up: layer 0 update fused with its forward, then the read-only layers
+    forward(0, 0, cur ^ 1, 1, m);
+    trace(300);
+    bar.sync_local();
+    trace(400);
+    for (int l = 1; l < NL; ++l) {
+      forward(l, cur ^ 1, cur ^ 1, 0, m);
+      trace(300 + l);
+      bar.sync_local();
+      trace(400 + l);
+    }
+    cur ^= 1;
+    st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, plast.r0, plast.cnt, dsl, nullptr, red);
+    trace(2);
+    dE = E - st.err;
+    E = st.err;
+    ok = (st.argmax == st.target);
+    if (iter == 1) first_ok = ok;
+    if (iter > p.max_iter) break;
+    ok = ok && (iter > p.min_iter);
+    if (!(dE > p.thr || !ok)) break;
+  }
+  // ---- write the pending factors back so that memory holds W_true again
+  if (m > 0) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < pmax; i += kThreads) dsl[i] = 0.0;  // lr == 0 and no sums are wanted
+    __syncthreads();
+    for (int l = 1; l < NL; ++l) {
+      const Panel pn = panel(l);
+      if (pn.cnt > 0)
+        panel_cols_flush(n.W[l], n.ld[l], pn, dsl, us_of(l), A + n.off_hist_v[l], act_of(l, cur), 0.0, m, nullptr);
+    }
+  }
+  if (b == 0) output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, 0, 0, nullptr, A + n.off_out, red);
+  bar.finish();
+  if (b == 0 && threadIdx.x == 0) n.local_sync[160] = ld_relaxed_gpu(n.local_sync + 160) + 1u;
+  if (b == 0 && threadIdx.x == 0 && p.result) {
+    hpnn_train_result r;
+    r.init_err = init_err;
+    r.final_de = dE;
+    r.last_err = E;
+    r.n_iter = iter;
+    r.first_ok = first_ok;
+    r.success = ok;
+    r.reserved = st.argmax;
+    *p.result = r;
+  }
+}
+
+// 0 = launched, < 0 = error, 1 = not eligible.  HPNN_LAZY_PANEL=0 falls back to the column-task
+// variant of train_lazy.cu (which also serves every multi-rank job).
+int g_lazy_panel = -1;  // -1 = HPNN_LAZY_PANEL (default on), 0 = off, 1 = on
+int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
+  static const int disabled_env = [] {
+    const char *e = getenv("HPNN_LAZY_PANEL");
+    return (e && !strcmp(e, "0")) ? 1 : 0;
+  }();
+  const int disabled = g_lazy_panel >= 0 ? !g_lazy_panel : disabled_env;
+  const int depth = lazy_depth_setting();
+  const hpnn_dev_net &n = p_in.net;
+  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || p_in.train != HPNN_TRAIN_BP || n.world != 1 ||
+      n.hist_depth < 2 || n.panel_stride <= 0 || n.n_layers < 2)
+    return 1;
+  KP p = p_in;
+  p.lazy_depth = depth < n.hist_depth ? depth : n.hist_depth;
+  int pmax = 1, rowpart = 8;
+  for (int l = 0; l < n.n_layers; ++l) {
+    const int pm = panel_max(n.dims[l + 1], grid);
+    pmax = pm > pmax ? pm : pmax;
+    const int d = row_part_doubles(n.dims[l + 1], grid);
+    rowpart = d > rowpart ? d : rowpart;
+  }
+  pmax = (pmax + 7) & ~7;
+  if (rowpart < pmax * 8) rowpart = pmax * 8;
+  p.max_rows = pmax;  // the kernel's carve-up uses the panel height, not the layer height
+  const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart);
+  if (smem > 227 * 1024) return 1;
+  cudaError_t e = cudaFuncSetAttribute((const void *)k_train_sample_lazy1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(k_train_sample_lazy1)", e);
+    return -1;
+  }
+  void *args[] = {(void *)&p};
+  e = cudaLaunchCooperativeKernel((const void *)k_train_sample_lazy1, dim3(grid), dim3(kThreads), args, smem,
+                                  (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("cudaLaunchCooperativeKernel(k_train_sample_lazy1)", e);
+    return -1;
+  }
+  return 0;
+}
+
+}  // namespace hpnn
+
+extern "C" void hpnn_dev_set_lazy_panel(int on) { hpnn::g_lazy_panel = on < 0 ? -1 : (on ? 1 : 0); }

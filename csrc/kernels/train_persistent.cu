@@ -203,6 +203,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
 int launch_resident_if_eligible(const KP &p, int grid, void *stream);
 // defined in train_lazy.cu, same convention
 int launch_lazy_if_eligible(const KP &p, int grid, size_t smem, void *stream);
+// defined in train_lazy1.cu (one GPU, row panels), same convention
+int launch_lazy1_if_eligible(const KP &p, int grid, void *stream);
 extern long long g_lazy_min_bytes;
 
 // ------------------------------- host side ---------------------------------
@@ -308,6 +310,15 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
       }
     }
   }
+  net->off_panel = 0;
+  net->panel_stride = 0;
+  if (net->hist_depth > 0 && W == 1) {
+    int wide = 8;
+    for (int l = 1; l < NL; ++l) wide = net->ld[l] > wide ? net->ld[l] : wide;
+    net->panel_stride = wide + kLazyChunk;
+    net->off_panel = off;
+    off += 2LL * kLazyDotSlots * net->panel_stride;
+  }
   net->arena_doubles = off;
   return off;
 }
@@ -362,6 +373,13 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
     rowpart = d > rowpart ? d : rowpart;
   }
   const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles + rowpart);
+  {
+    const int rc = launch_lazy1_if_eligible(p, grid, stream);
+    if (rc <= 0) {
+      if (rc == 0) ++g_launches;
+      return rc;
+    }
+  }
   if (smem <= 227 * 1024) {
     // BP on layers far larger than L2: deferred rank-1 updates save most of the write-back traffic
     const int rc = launch_lazy_if_eligible(p, grid, smem, stream);

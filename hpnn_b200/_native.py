@@ -46,7 +46,7 @@ class DevNet(C.Structure):
                 ("off_cta_part", C.c_longlong * MAX_LAYERS), ("cta_slots", C.c_int),
                 ("off_hist_u", C.c_longlong * MAX_LAYERS), ("off_hist_v", C.c_longlong * MAX_LAYERS),
                 ("off_hist_dot", C.c_longlong * MAX_LAYERS),
-                ("hist_depth", C.c_int)]
+                ("hist_depth", C.c_int), ("off_panel", C.c_longlong), ("panel_stride", C.c_int)]
 
 
 _lib = None
@@ -105,6 +105,7 @@ def _declare(lib):
         "hpnn_dev_persistent_grid": (i, []),
         "hpnn_dev_set_persistent_grid": (None, [i]),
         "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),
+        "hpnn_dev_set_lazy_panel": (None, [i]),
         "hpnn_dev_set_phase_trace": (None, [vp, i]),
         "hpnn_dev_forward_layer": (i, [vp, i, i, i, vp, vp, i, vp]),
         "hpnn_dev_output_stats": (i, [i, i, vp, vp, i, vp, vp, vp, vp]),

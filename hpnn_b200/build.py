@@ -33,6 +33,7 @@ CORE_SOURCES = [
     "csrc/kernels/train_persistent.cu",
     "csrc/kernels/train_resident.cu",
     "csrc/kernels/train_lazy.cu",
+    "csrc/kernels/train_lazy1.cu",
     "csrc/kernels/ops.cu",
     "csrc/kernels/gemm_umma.cu",
     "csrc/kernels/noalloc.cu",

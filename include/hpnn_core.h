@@ -174,6 +174,10 @@ typedef struct {
   /* per-(rank, CTA) partial dot products v_j . x of layer l >= 1, world x 160 chunks of 8 */
   long long off_hist_dot[HPNN_MAX_LAYERS];
   int hist_depth;
+  /* single rank: per-CTA partial W^T.delta vectors of the row-panel variant (train_lazy1.cu),
+   * 2 buffers x 160 CTAs x panel_stride doubles (panel_stride = widest ld + 8; 0 = none) */
+  long long off_panel;
+  int panel_stride;
 } hpnn_dev_net;
 
 /* Deferred-update BP trainer for layers much larger than L2 (train_lazy.cu).  depth: write-back
@@ -181,6 +185,9 @@ typedef struct {
  * min_bytes: smallest local weight volume of the layers >= 1 for which hpnn_dev_arena_layout
  * reserves the factor history (-1 = default 64 MiB); set it BEFORE laying out a network. */
 void hpnn_dev_set_lazy(int depth, long long min_bytes);
+/* one rank only: row-panel organisation of the same trainer (train_lazy1.cu); 1 = on, 0 = off
+ * (column tasks, train_lazy.cu), -1 = default (on unless HPNN_LAZY_PANEL=0) */
+void hpnn_dev_set_lazy_panel(int on);
 
 /* fills ld/row0/rows/offsets from dims/rank/world; returns arena size in doubles */
 long long hpnn_dev_arena_layout(hpnn_dev_net *net);

@@ -105,14 +105,16 @@ def test_multi_launch_path_with_logical_ranks(world, nn_type, train):
     np.testing.assert_allclose(eng.run(X[0]), cpu.run(X[0]), atol=1e-12)
 
 
+@pytest.mark.parametrize("panel", [0, 1])
 @pytest.mark.parametrize("depth", [2, 3, 8])
 @pytest.mark.parametrize("nn_type", [N.TYPE_ANN, N.TYPE_SNN])
-def test_deferred_update_trainer_matches_cpu_engine(depth, nn_type):
+def test_deferred_update_trainer_matches_cpu_engine(depth, nn_type, panel):
     """K-PL (train_lazy.cu) keeps the rank-1 updates of the layers >= 1 in factored form and writes
     them back every `depth` iterations; a fixed iteration count must reproduce the CPU engine's
     weights to round-off, whatever the count is relative to the write-back period."""
     lib = N.load()
     lib.hpnn_dev_set_lazy(depth, 0)  # reserve the factor history for every shape
+    lib.hpnn_dev_set_lazy_panel(panel)  # 1: row panels (train_lazy1.cu), 0: column tasks (train_lazy.cu)
     try:
         k, _ = hp.generate_kernel(77, 40, [600, 300, 150], 12)
         X, T = make_problem(nn_type, 40, (600, 300, 150), 12, n_samples=3, seed=3)
@@ -133,3 +135,4 @@ def test_deferred_update_trainer_matches_cpu_engine(depth, nn_type):
             cpu.close()
     finally:
         lib.hpnn_dev_set_lazy(-1, -1)
+        lib.hpnn_dev_set_lazy_panel(-1)
