@@ -171,24 +171,125 @@ __device__ __forceinline__ void panel_cols_flush(double *W, int ld, Panel pn, co
   }
 }
 
+// sums of 8 values over the 32 lanes with 9 exchanges instead of 40: every step halves the number
+// of values a lane is responsible for.  Returns the complete sum of value ((lane >> 2) & 7).
+__device__ __forceinline__ double reduce8(const double (&pr)[8], int lane) {
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+  double s4[4], s2[2];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const double keep = b4 ? pr[4 + q] : pr[q], give = b4 ? pr[q] : pr[4 + q];
+    s4[q] = keep + __shfl_xor_sync(0xffffffffu, give, 16);
+  }
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const double keep = b3 ? s4[2 + q] : s4[q], give = b3 ? s4[q] : s4[2 + q];
+    s2[q] = keep + __shfl_xor_sync(0xffffffffu, give, 8);
+  }
+  const double keep = b2 ? s2[1] : s2[0], give = b2 ? s2[0] : s2[1];
+  double s1 = keep + __shfl_xor_sync(0xffffffffu, give, 4);
+  s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+  s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
+  return s1;
+}
+
+constexpr int kZStride = kWarps;  // partial dot products per row kept in shared memory (>= 8 segments)
+
+// z partials of the own panel, streaming variant for wide layers: like the top-down pass the CTA
+// walks its rows one after the other, every thread holding the x values of four column pairs per
+// group; the per-row sums are completed inside each warp (reduce8) and parked per warp in
+// zpart[i*kZStride + warp] -- no CTA-wide barrier until the whole panel is done.
+template <int UPD>
+__device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, const double *xs, const double *dsl,
+                                               double lr, double *zpart) {
+  constexpr int G = 4;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double2 zero2 = make_double2(0.0, 0.0);
+  for (int i = lane; i < pn.cnt; i += 32) zpart[i * kZStride + warp] = 0.0;  // own slots only
+  __syncwarp();
+  for (int g0 = 0; g0 < ld; g0 += G * kPanelCols) {
+    const int cbase = g0 + 2 * threadIdx.x;
+    double2 xr[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      const int c = cbase + k * kPanelCols;
+      xr[k] = (c < ld) ? *reinterpret_cast<const double2 *>(xs + c) : zero2;
+    }
+    double2 wa[G], wb[G];
+    auto load = [&](double2 (&w)[G], int i) {
+      const double *row = W + (size_t)(pn.r0 + i) * ld;
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        const int c = cbase + k * kPanelCols;
+        w[k] = (i < pn.cnt && c < ld) ? ldg_cg2(reinterpret_cast<const double2 *>(row + c)) : zero2;
+      }
+    };
+    auto consume = [&](double2 (&w)[G], int i) -> double {
+      double a = 0.0, b = 0.0;
+      if (UPD && i < pn.cnt) {
+        const double s = lr * dsl[i];
+        double *row = W + (size_t)(pn.r0 + i) * ld;
+#pragma unroll
+        for (int k = 0; k < G; ++k) {
+          const int c = cbase + k * kPanelCols;
+          if (c < ld) {
+            w[k].x = fma(s, xr[k].x, w[k].x);
+            w[k].y = fma(s, xr[k].y, w[k].y);
+            stg_cg2(reinterpret_cast<double2 *>(row + c), w[k]);
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        a = fma(w[k].x, xr[k].x, a);
+        b = fma(w[k].y, xr[k].y, b);
+      }
+      return a + b;
+    };
+    load(wa, 0);
+    load(wb, 1);
+    for (int i0 = 0; i0 < pn.cnt; i0 += 8) {
+      double pr[8];
+#pragma unroll
+      for (int u = 0; u < 8; u += 2) {
+        pr[u] = consume(wa, i0 + u);
+        load(wa, i0 + u + 2);
+        pr[u + 1] = consume(wb, i0 + u + 1);
+        load(wb, i0 + u + 3);
+      }
+      const double s = reduce8(pr, lane);
+      const int i = i0 + ((lane >> 2) & 7);
+      if ((lane & 3) == 0 && i < pn.cnt) zpart[i * kZStride + warp] += s;
+    }
+  }
+}
+
 // Row tasks over the own panel.
-//   UPD 0: z_i = S[r,:].x + sum_j us[i][j] coef[j]      (read-only; us == nullptr or m == 0: plain)
-//   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                (layer 0)
-// y goes to out[r]; while it is at hand the CTA's share of the next layer's v_j . y is formed.
+//   UPD 0: z_i = S[r,:].x + sum_{j<mcorr} us[i][j] coef[j]   (read-only; us == nullptr: plain)
+//   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                     (immediate update; unused by K-PL1)
+// y goes to out[r]; while it is at hand the CTA's share of the next layer's v_j . y (j < m) is formed.
 template <int UPD>
 __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
-                                           int act_kind, double *out, int segs, double *rowpart, const double *us,
-                                           const double *coef, int m, const DotOut &dots, double *red) {
+                                           int act_kind, double *out, int segs, double *zpart, const double *us,
+                                           const double *coef, int mcorr, int m, const DotOut &dots, double *red) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n2 = ld >> 1;
-  const int seg2 = (n2 + segs - 1) / segs;
-  for (int u = warp; u < pn.cnt * segs; u += kWarps) {
-    const int i = u / segs, sg = u % segs;
-    const int c0 = sg * seg2, c1 = min(n2, c0 + seg2);
-    double *wrow = W + (size_t)(pn.r0 + i) * ld + 2 * c0;
-    const double s = UPD ? lr * dsl[i] : 0.0;
-    const double z = c1 > c0 ? warp_row<UPD>(wrow, nullptr, xs + 2 * c0, 2 * (c1 - c0), s, 0.0, lane) : 0.0;
-    if (lane == 0) rowpart[i * 8 + sg] = z;
+  int nz;  // partials per row
+  if (ld >= 4 * kPanelCols) {
+    panel_z_stream<UPD>(W, ld, pn, xs, dsl, lr, zpart);
+    nz = kWarps;
+  } else {
+    // narrow layers: one warp per (row, segment), see phase_rows
+    const int n2 = ld >> 1;
+    const int seg2 = (n2 + segs - 1) / segs;
+    for (int u = warp; u < pn.cnt * segs; u += kWarps) {
+      const int i = u / segs, sg = u % segs;
+      const int c0 = sg * seg2, c1 = min(n2, c0 + seg2);
+      double *wrow = W + (size_t)(pn.r0 + i) * ld + 2 * c0;
+      const double s = UPD ? lr * dsl[i] : 0.0;
+      const double z = c1 > c0 ? warp_row<UPD>(wrow, nullptr, xs + 2 * c0, 2 * (c1 - c0), s, 0.0, lane) : 0.0;
+      if (lane == 0) zpart[i * kZStride + sg] = z;
+    }
+    nz = segs;
   }
   __syncthreads();
   const bool want_dots = dots.p[0] != nullptr && m > 0 && pn.cnt > 0;
@@ -197,10 +298,10 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
   for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
   for (int i = threadIdx.x; i < pn.cnt; i += blockDim.x) {
     double z = 0.0;
-    for (int sg = 0; sg < segs; ++sg) z += rowpart[i * 8 + sg];
-    if (!UPD && us && m > 0) {
+    for (int q = 0; q < nz; ++q) z += zpart[i * kZStride + q];
+    if (!UPD && us && mcorr > 0) {
       double corr = 0.0;
-      for (int j = 0; j < m; ++j) corr = fma(us[(size_t)i * kLazyChunk + j], coef[j], corr);
+      for (int j = 0; j < mcorr; ++j) corr = fma(us[(size_t)i * kLazyChunk + j], coef[j], corr);
       z += corr;
     }
     const double y = act_kind == 0 ? act_f(z) : z;
@@ -251,7 +352,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   // per-CTA slots: partial column sums (+ 8 partial u_j . delta behind them), two buffers
   auto pslot = [&](int buf, int cta) { return A + n.off_panel + ((size_t)buf * kLazyDotSlots + cta) * n.panel_stride; };
 
-  auto forward = [&](int l, int src_buf, int dst_buf, int u, int m) {
+  // Layer 0 sees the same input x in every iteration, so its pending updates collapse into ONE
+  // factor pair: W0_true = S0 + ubar (x) x with ubar = sum of lr*delta_0 so far (slot 0 of the
+  // layer's u chunks), z = S0.x + ubar*(x.x).  W0 is read-only until the end of the sample.
+  __shared__ double coef0[kLazyChunk];
+  {
+    const double *x0 = act_of(0, 0);
+    double s = 0.0;
+    for (int c = threadIdx.x; c < n.dims[0]; c += kThreads) {
+      const double v = ldg_cg(x0 + c);
+      s = fma(v, v, s);
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x < kLazyChunk) coef0[threadIdx.x] = threadIdx.x == 0 ? s : 0.0;
+    for (int i = threadIdx.x; i < pmax; i += kThreads) us[(size_t)i * kLazyChunk] = 0.0;
+    __syncthreads();
+  }
+  auto forward = [&](int l, int src_buf, int dst_buf, int m) {
     stage_vec(xs, act_of(l, src_buf), pad8(n.dims[l]));
     __syncthreads();
     if (l >= 1 && m > 0) gather_dots(n, l, m, coef, red);  // coef[j] = v_j . x
@@ -265,12 +382,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     }
     const int kind = (snn && l == NL - 1) ? 1 : 0;
     const int segs = pick_row_segments(n.dims[l + 1], n.ld[l], grid);
-    if (u) panel_rows<1>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, act_of(l + 1, dst_buf), segs, rowpart, nullptr, coef, m, dots, red);
-    else panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, act_of(l + 1, dst_buf), segs, rowpart, l >= 1 ? us_of(l) : nullptr, coef, m, dots, red);
+    panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, act_of(l + 1, dst_buf), segs, rowpart, us_of(l),
+                  l == 0 ? coef0 : coef, l == 0 ? 1 : m, m, dots, red);
   };
 
   for (int l = 0; l < NL; ++l) {
-    forward(l, cur, cur, 0, 0);
+    forward(l, cur, cur, 0);
     bar.sync_local();
   }
   const double *target = A + n.off_target;
@@ -331,8 +448,18 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
       for (int ci0 = 0; ci0 < below.cnt; ci0 += 64) {
         const int ci = ci0 + (threadIdx.x & 63), g = threadIdx.x >> 6;
         double s = 0.0;
-        if (ci < below.cnt)
-          for (int q = g; q < nbp; q += kThreads / 64) s += ldg_cg(pslot(l & 1, q) + below.r0 + ci);
+        if (ci < below.cnt) {
+          // all (<= 20) partials of this thread in flight at once, added in CTA order
+          constexpr int NQ = kLazyDotSlots / (kThreads / 64);
+          double v[NQ];
+#pragma unroll
+          for (int k = 0; k < NQ; ++k) {
+            const int q = g + k * (kThreads / 64);
+            v[k] = (q < nbp) ? ldg_cg(pslot(l & 1, q) + below.r0 + ci) : 0.0;
+          }
+#pragma unroll
+          for (int k = 0; k < NQ; ++k) s += v[k];
+        }
         __syncthreads();
         red[threadIdx.x] = s;
         __syncthreads();
@@ -349,12 +476,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     }
     m = flush ? 0 : m + 1;
     // ---- bottom-up: layer 0 update fused with its forward, then the read-only layers
-    forward(0, 0, cur ^ 1, 1, m);
+    {
+      const Panel p0 = panel(0);
+      for (int i = threadIdx.x; i < p0.cnt; i += kThreads) us[(size_t)i * kLazyChunk] += p.lr * dsl[i];  // ubar
+    }
+    forward(0, 0, cur ^ 1, m);  // (stages x and synchronises before ubar is read)
     trace(300);
     bar.sync_local();
     trace(400);
     for (int l = 1; l < NL; ++l) {
-      forward(l, cur ^ 1, cur ^ 1, 0, m);
+      forward(l, cur ^ 1, cur ^ 1, m);
       trace(300 + l);
       bar.sync_local();
       trace(400 + l);
@@ -371,6 +502,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     if (!(dE > p.thr || !ok)) break;
   }
   // ---- write the pending factors back so that memory holds W_true again
+  {  // layer 0: S0 += ubar (x) x, one warp per own row
+    const Panel p0 = panel(0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    stage_vec(xs, act_of(0, 0), pad8(n.dims[0]));
+    __syncthreads();
+    const double2 *x2 = reinterpret_cast<const double2 *>(xs);
+    for (int i = warp; i < p0.cnt; i += kWarps) {
+      const double ub = us[(size_t)i * kLazyChunk];
+      double2 *w2 = reinterpret_cast<double2 *>(n.W[0] + (size_t)(p0.r0 + i) * n.ld[0]);
+      for (int c = lane; c < (n.ld[0] >> 1); c += 32) {
+        double2 w = ldg_cg2(w2 + c);
+        w.x = fma(ub, x2[c].x, w.x);
+        w.y = fma(ub, x2[c].y, w.y);
+        stg_cg2(w2 + c, w);
+      }
+    }
+  }
   if (m > 0) {
     __syncthreads();
     for (int i = threadIdx.x; i < pmax; i += kThreads) dsl[i] = 0.0;  // lr == 0 and no sums are wanted
@@ -421,7 +569,7 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
     rowpart = d > rowpart ? d : rowpart;
   }
   pmax = (pmax + 7) & ~7;
-  if (rowpart < pmax * 8) rowpart = pmax * 8;
+  rowpart = pmax * kZStride;
   p.max_rows = pmax;  // the kernel's carve-up uses the panel height, not the layer height
   const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart);
   if (smem > 227 * 1024) return 1;

@@ -115,24 +115,28 @@ def test_deferred_update_trainer_matches_cpu_engine(depth, nn_type, panel):
     lib = N.load()
     lib.hpnn_dev_set_lazy(depth, 0)  # reserve the factor history for every shape
     lib.hpnn_dev_set_lazy_panel(panel)  # 1: row panels (train_lazy1.cu), 0: column tasks (train_lazy.cu)
+    # the second shape has a layer wider than 4096 columns (streaming forward pass of the panel
+    # variant, with a partially filled second column group) and more rows than CTAs
+    shapes = [(40, (600, 300, 150), 12)] if depth != 8 else [(40, (600, 300, 150), 12), (24, (4200, 310), 10)]
     try:
-        k, _ = hp.generate_kernel(77, 40, [600, 300, 150], 12)
-        X, T = make_problem(nn_type, 40, (600, 300, 150), 12, n_samples=3, seed=3)
-        for n_it in (1, 7, 16, 37):
-            kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
-            gpu = CudaEngine(k, nn_type, N.TRAIN_BP, **kw)
-            assert gpu.net.net.hist_depth == 8
-            cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw)
-            for x, t in zip(X, T):
-                rg, rc = gpu.train(x, t), cpu.train(x, t)
-                assert rg.n_iter == rc.n_iter == n_it
-                assert abs(rg.init_err - rc.init_err) < 1e-12
-                assert abs(rg.last_err - rc.last_err) < 1e-11
-            for a, b in zip(gpu.kernel().weights, cpu.kernel().weights):
-                np.testing.assert_allclose(a, b, atol=1e-11)
-            np.testing.assert_allclose(gpu.run(X[0]), cpu.run(X[0]), atol=1e-10)
-            gpu.close()
-            cpu.close()
+        for n_in, hid, n_out in shapes:
+            k, _ = hp.generate_kernel(77, n_in, list(hid), n_out)
+            X, T = make_problem(nn_type, n_in, hid, n_out, n_samples=3, seed=3)
+            for n_it in (1, 7, 16, 37):
+                kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
+                gpu = CudaEngine(k, nn_type, N.TRAIN_BP, **kw)
+                assert gpu.net.net.hist_depth == 8
+                cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw)
+                for x, t in zip(X, T):
+                    rg, rc = gpu.train(x, t), cpu.train(x, t)
+                    assert rg.n_iter == rc.n_iter == n_it
+                    assert abs(rg.init_err - rc.init_err) < 1e-12
+                    assert abs(rg.last_err - rc.last_err) < 1e-11
+                for a, b in zip(gpu.kernel().weights, cpu.kernel().weights):
+                    np.testing.assert_allclose(a, b, atol=1e-11)
+                np.testing.assert_allclose(gpu.run(X[0]), cpu.run(X[0]), atol=1e-10)
+                gpu.close()
+                cpu.close()
     finally:
         lib.hpnn_dev_set_lazy(-1, -1)
         lib.hpnn_dev_set_lazy_panel(-1)
