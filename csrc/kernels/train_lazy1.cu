@@ -267,10 +267,10 @@ __device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, cons
 // Row tasks over the own panel.
 //   UPD 0: z_i = S[r,:].x + sum_{j<mcorr} us[i][j] coef[j]   (read-only; us == nullptr: plain)
 //   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                     (immediate update; unused by K-PL1)
-// y goes to out[r]; while it is at hand the CTA's share of the next layer's v_j . y (j < m) is formed.
+// y goes to every rank's activation buffer (dst); while it is at hand the CTA's share of the next layer's v_j . y (j < m) is formed.
 template <int UPD>
 __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
-                                           int act_kind, double *out, int segs, double *zpart, const double *us,
+                                           int act_kind, const Dst &dst, int segs, double *zpart, const double *us,
                                            const double *coef, int mcorr, int m, const DotOut &dots, double *red) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int nz;  // partials per row
@@ -305,13 +305,14 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
       z += corr;
     }
     const double y = act_kind == 0 ? act_f(z) : z;
-    stg_cg(out + pn.r0 + i, y);
-    if (want_dots) chunk_fma(dots.HV + (size_t)(pn.r0 + i) * kLazyChunk, y, m, acc);
+    dst_store(dst, pn.r0 + i, y);
+    if (want_dots) chunk_fma(dots.HV + (size_t)(dots.row0 + pn.r0 + i) * kLazyChunk, y, m, acc);
   }
   if (want_dots) {  // CTA-uniform
     __shared__ double mine_dots[kLazyChunk];
     chunk_block_sum(acc, m, mine_dots, red);
-    if (threadIdx.x < kLazyChunk) stg_cg(dots.p[0] + threadIdx.x, mine_dots[threadIdx.x]);
+    if (threadIdx.x < kLazyChunk)
+      for (int q = 0; q < dots.n; ++q) stg_cg(dots.p[q] + threadIdx.x, mine_dots[threadIdx.x]);
   }
 }
 
@@ -329,9 +330,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   __shared__ double coef[kLazyChunk];
 
   const int n_out = n.dims[NL];
-  double *A = n.arena[0];
+  double *A = n.arena[n.rank];
   const bool snn = p.type == HPNN_TYPE_SNN;
   const int depth = p.lazy_depth;
+  const bool multi = n.world > 1;
 
   Barrier bar;
   bar.init(n);
@@ -344,10 +346,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     }
   };
   int cur = 0;
-  auto act_of = [&](int i, int buf) -> double * {
-    return A + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]));
+  auto act_peer = [&](int q, int i, int buf) -> double * {
+    return n.arena[q] + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]));
   };
-  auto panel = [&](int l) { return panel_of(n.dims[l + 1], grid, b); };
+  auto act_of = [&](int i, int buf) -> double * { return act_peer(n.rank, i, buf); };
+  auto panel = [&](int l) { return panel_of(n.rows[l], grid, b); };  // local row indices of this rank's block
   auto us_of = [&](int l) { return us + (size_t)l * pmax * kLazyChunk; };
   // per-CTA slots: partial column sums (+ 8 partial u_j . delta behind them), two buffers
   auto pslot = [&](int buf, int cta) { return A + n.off_panel + ((size_t)buf * kLazyDotSlots + cta) * n.panel_stride; };
@@ -372,28 +375,34 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     stage_vec(xs, act_of(l, src_buf), pad8(n.dims[l]));
     __syncthreads();
     if (l >= 1 && m > 0) gather_dots(n, l, m, coef, red);  // coef[j] = v_j . x
+    Dst dst;  // all-gather by peer stores
+    dst.n = n.world;
+    dst.tag = 0ull;
+    for (int q = 0; q < n.world; ++q) dst.p[q] = act_peer(q, l + 1, dst_buf) + (size_t)n.row0[l];
     DotOut dots;
-    dots.n = 1;
+    dots.n = n.world;
     dots.p[0] = nullptr;
     if (l + 1 < NL && m > 0) {
-      dots.p[0] = A + n.off_hist_dot[l + 1] + (size_t)b * kLazyChunk;
+      for (int q = 0; q < n.world; ++q)
+        dots.p[q] = n.arena[q] + n.off_hist_dot[l + 1] + (size_t)(n.rank * kLazyDotSlots + b) * kLazyChunk;
       dots.HV = A + n.off_hist_v[l + 1];
-      dots.row0 = 0;
+      dots.row0 = n.row0[l];
     }
     const int kind = (snn && l == NL - 1) ? 1 : 0;
-    const int segs = pick_row_segments(n.dims[l + 1], n.ld[l], grid);
-    panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, act_of(l + 1, dst_buf), segs, rowpart, us_of(l),
+    const int segs = pick_row_segments(n.rows[l], n.ld[l], grid);
+    panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, dst, segs, rowpart, us_of(l),
                   l == 0 ? coef0 : coef, l == 0 ? 1 : m, m, dots, red);
   };
 
   for (int l = 0; l < NL; ++l) {
     forward(l, cur, cur, 0);
-    bar.sync_local();
+    bar.sync_all(n, panel(l).cnt > 0);
   }
   const double *target = A + n.off_target;
   const int last = NL - 1;
   const Panel plast = panel(last);
-  OutStats st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, plast.r0, plast.cnt, dsl, nullptr, red);
+  const int out_row0 = n.row0[last] + plast.r0;
+  OutStats st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, out_row0, plast.cnt, dsl, nullptr, red);
   double E = st.err;
   const double init_err = E;
   int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
@@ -433,29 +442,34 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
       trace(100 + l);
       bar.sync_local();
       trace(200 + l);
-      // ---- reduce: deltas of the own panel of layer l-1 from everybody's partial sums
-      const int nbp = grid < n.dims[l + 1] ? grid : n.dims[l + 1];  // CTAs that own rows of layer l
+      // ---- reduce: this rank's partial sums, column slice by column slice.  One rank: the slice
+      // of CTA b is its own panel of the layer below, so the deltas are finished here.  Several
+      // ranks: the slice sums go to the rank owning that row of the layer below (reduce-scatter by
+      // peer stores into the part slots of K-P), and after the cross-rank barrier the owning CTA
+      // adds one value per rank.
+      const int nbp = grid < n.rows[l] ? grid : n.rows[l];  // CTAs of this rank that own rows of layer l
       if (m > 0) {
         double acc[kLazyChunk];
 #pragma unroll
         for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
         for (int q = threadIdx.x; q < nbp; q += kThreads)
           chunk_fma(pslot(l & 1, q) + n.panel_stride - kLazyChunk, 1.0, m, acc);
-        chunk_block_sum(acc, m, coef, red);  // coef[j] = u_j . delta_l
+        chunk_block_sum(acc, m, coef, red);  // coef[j] = u_j . delta_l over this rank's rows
       }
-      const Panel below = panel(l - 1);
-      const double *hb = act_of(l, cur);  // output of layer l-1
-      for (int ci0 = 0; ci0 < below.cnt; ci0 += 64) {
+      const Panel slice = panel_of(n.dims[l], grid, b);  // columns of layer l == rows of layer l-1 (global)
+      const double *hb = act_of(l, cur);                   // output of layer l-1
+      const int cols = n.dims[l];
+      for (int ci0 = 0; ci0 < slice.cnt; ci0 += 64) {
         const int ci = ci0 + (threadIdx.x & 63), g = threadIdx.x >> 6;
         double s = 0.0;
-        if (ci < below.cnt) {
+        if (ci < slice.cnt) {
           // all (<= 20) partials of this thread in flight at once, added in CTA order
           constexpr int NQ = kLazyDotSlots / (kThreads / 64);
           double v[NQ];
 #pragma unroll
           for (int k = 0; k < NQ; ++k) {
             const int q = g + k * (kThreads / 64);
-            v[k] = (q < nbp) ? ldg_cg(pslot(l & 1, q) + below.r0 + ci) : 0.0;
+            v[k] = (q < nbp) ? ldg_cg(pslot(l & 1, q) + slice.r0 + ci) : 0.0;
           }
 #pragma unroll
           for (int k = 0; k < NQ; ++k) s += v[k];
@@ -463,13 +477,31 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
         __syncthreads();
         red[threadIdx.x] = s;
         __syncthreads();
-        if (threadIdx.x < 64 && ci < below.cnt) {
+        if (threadIdx.x < 64 && ci < slice.cnt) {
           double pc = 0.0;
 #pragma unroll
           for (int gg = 0; gg < kThreads / 64; ++gg) pc += red[gg * 64 + threadIdx.x];
-          const int c = below.r0 + ci;
+          const int c = slice.r0 + ci;
           if (m > 0) pc += chunk_apply(HV + (size_t)c * kLazyChunk, coef, m);
-          dsl[ci] = pc * dact_f(ldg_cg(hb + c));
+          if (!multi) {
+            dsl[ci] = pc * dact_f(ldg_cg(hb + c));
+          } else {
+            const int own = owner_of_row(c, cols, n.world);
+            stg_cg(n.arena[own] + n.off_part[l - 1] + (size_t)(n.rank * kMaxRsplit) * n.part_stride[l - 1] +
+                       (c - row0_of(own, cols, n.world)),
+                   pc);
+          }
+        }
+      }
+      if (multi) {
+        bar.sync_all(n, slice.cnt > 0);
+        trace(500 + l);
+        const Panel below = panel(l - 1);
+        const double *part = A + n.off_part[l - 1];
+        for (int i = threadIdx.x; i < below.cnt; i += kThreads) {
+          double s = 0.0;
+          for (int g = 0; g < n.world; ++g) s += ldg_cg(part + (size_t)(g * kMaxRsplit) * n.part_stride[l - 1] + below.r0 + i);
+          dsl[i] = s * dact_f(ldg_cg(hb + n.row0[l - 1] + below.r0 + i));
         }
       }
       __syncthreads();
@@ -482,16 +514,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     }
     forward(0, 0, cur ^ 1, m);  // (stages x and synchronises before ubar is read)
     trace(300);
-    bar.sync_local();
+    bar.sync_all(n, panel(0).cnt > 0);
     trace(400);
     for (int l = 1; l < NL; ++l) {
       forward(l, cur ^ 1, cur ^ 1, m);
       trace(300 + l);
-      bar.sync_local();
+      bar.sync_all(n, panel(l).cnt > 0);
       trace(400 + l);
     }
     cur ^= 1;
-    st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, plast.r0, plast.cnt, dsl, nullptr, red);
+    st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, out_row0, plast.cnt, dsl, nullptr, red);
     trace(2);
     dE = E - st.err;
     E = st.err;
@@ -556,17 +588,15 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
   const int disabled = g_lazy_panel >= 0 ? !g_lazy_panel : disabled_env;
   const int depth = lazy_depth_setting();
   const hpnn_dev_net &n = p_in.net;
-  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || p_in.train != HPNN_TRAIN_BP || n.world != 1 ||
+  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || p_in.train != HPNN_TRAIN_BP || p_in.tagged ||
       n.hist_depth < 2 || n.panel_stride <= 0 || n.n_layers < 2)
     return 1;
   KP p = p_in;
   p.lazy_depth = depth < n.hist_depth ? depth : n.hist_depth;
   int pmax = 1, rowpart = 8;
   for (int l = 0; l < n.n_layers; ++l) {
-    const int pm = panel_max(n.dims[l + 1], grid);
+    const int pm = panel_max(n.rows[l], grid);
     pmax = pm > pmax ? pm : pmax;
-    const int d = row_part_doubles(n.dims[l + 1], grid);
-    rowpart = d > rowpart ? d : rowpart;
   }
   pmax = (pmax + 7) & ~7;
   rowpart = pmax * kZStride;

@@ -312,7 +312,7 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
   }
   net->off_panel = 0;
   net->panel_stride = 0;
-  if (net->hist_depth > 0 && W == 1) {
+  if (net->hist_depth > 0) {
     int wide = 8;
     for (int l = 1; l < NL; ++l) wide = net->ld[l] > wide ? net->ld[l] : wide;
     net->panel_stride = wide + kLazyChunk;

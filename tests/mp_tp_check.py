@@ -79,28 +79,31 @@ def main():
     lib = N.load()
     os.environ["HPNN_TP_PROTOCOL"] = "barrier"  # the variant uses the fence + flag barrier protocol
     lib.hpnn_dev_set_lazy(8, 0)
-    for nn_type in (N.TYPE_ANN, N.TYPE_SNN):
-        k, _ = hp.generate_kernel(31, 72, [520, 264, 130], 10)
-        X, T = problem(nn_type, 72, 10, 2, 17)
-        for n_it in (5, 19):
-            kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
-            lazy = CudaEngine(k, nn_type, N.TRAIN_BP, group=group, **kw)
-            assert lazy.net.net.hist_depth == 8
-            cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw) if rank == 0 else None
-            e_err = 0.0
-            for x, t in zip(X, T):
-                rl = lazy.train(x, t)
+    for panel in (1, 0):  # row panels (train_lazy1.cu) / column tasks (train_lazy.cu)
+        lib.hpnn_dev_set_lazy_panel(panel)
+        for nn_type in (N.TYPE_ANN, N.TYPE_SNN):
+            k, _ = hp.generate_kernel(31, 72, [520, 264, 130], 10)
+            X, T = problem(nn_type, 72, 10, 2, 17)
+            for n_it in (5, 19):
+                kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
+                lazy = CudaEngine(k, nn_type, N.TRAIN_BP, group=group, **kw)
+                assert lazy.net.net.hist_depth == 8
+                cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw) if rank == 0 else None
+                e_err = 0.0
+                for x, t in zip(X, T):
+                    rl = lazy.train(x, t)
+                    if rank == 0:
+                        r0 = cpu.train(x, t)
+                        e_err = max(e_err, abs(rl.last_err - r0.last_err), float(abs(rl.n_iter - r0.n_iter)))
+                kl = lazy.kernel()
                 if rank == 0:
-                    r0 = cpu.train(x, t)
-                    e_err = max(e_err, abs(rl.last_err - r0.last_err), float(abs(rl.n_iter - r0.n_iter)))
-            kl = lazy.kernel()
-            if rank == 0:
-                e_w = max(float(np.abs(a - b).max()) for a, b in zip(kl.weights, cpu.kernel().weights))
-                print(f"case deferred-update type={nn_type} iters={n_it} world={world}: max|dW|={e_w:.2e} "
-                      f"max|dE|={e_err:.2e}", flush=True)
-                if not (e_w < 1e-11 and e_err < 1e-11):
-                    fails += 1
-            lazy.close()
+                    e_w = max(float(np.abs(a - b).max()) for a, b in zip(kl.weights, cpu.kernel().weights))
+                    print(f"case deferred-update panel={panel} type={nn_type} iters={n_it} world={world}: "
+                          f"max|dW|={e_w:.2e} max|dE|={e_err:.2e}", flush=True)
+                    if not (e_w < 1e-11 and e_err < 1e-11):
+                        fails += 1
+                lazy.close()
+    lib.hpnn_dev_set_lazy_panel(-1)
     lib.hpnn_dev_set_lazy(-1, -1)
     del os.environ["HPNN_TP_PROTOCOL"]
     # ---- data-parallel gradient merge (extension): fused peer-load merge == NCCL all_reduce == serial sum
