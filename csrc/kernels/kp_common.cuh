@@ -19,6 +19,7 @@ struct KP {
   int max_ld, max_rows;  // shared-memory carve-up (doubles)
   int tagged;            // several ranks: tagged-pair hand-over instead of fence + flag barriers
   int lazy_depth;        // deferred-update trainer: weights are written back every lazy_depth iterations
+  long long prefetch_bytes;  // K-PL1: L2 prefetch volume per rank and barrier (0 = off)
   hpnn_train_result *result;
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;

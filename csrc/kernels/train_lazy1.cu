@@ -53,6 +53,14 @@ __host__ __device__ inline int panel_max(int rows, int grid) {
   return nb > 0 ? (rows + nb - 1) / nb : 0;
 }
 
+// Bulk L2 prefetch of one weight row.  Panel ownership is static, so while a CTA waits at a grid
+// (and cross-rank) barrier it already knows which rows it will stream next; with several ranks the
+// barrier lasts about as long as streaming a rank's share of a layer, so the HBM traffic of the
+// next phase hides behind the wait.
+__device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 constexpr int kPanelCols = 2 * kThreads;  // columns covered by one pass of the CTA (one double2 per thread)
 
 // Read-only top-down pass over the own panel: four column chunks per thread, rows outermost, two
@@ -352,6 +360,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   auto act_of = [&](int i, int buf) -> double * { return act_peer(n.rank, i, buf); };
   auto panel = [&](int l) { return panel_of(n.rows[l], grid, b); };  // local row indices of this rank's block
   auto us_of = [&](int l) { return us + (size_t)l * pmax * kLazyChunk; };
+  // first rows of the own panel of layer l into L2, at most p.prefetch_bytes per rank and call
+  auto prefetch_panel = [&](int l) {
+    if (threadIdx.x != 0 || l < 0 || l >= NL || p.prefetch_bytes <= 0) return;
+    const Panel pn = panel(l);
+    const long long row_bytes = 8LL * n.ld[l];
+    long long rows = p.prefetch_bytes / grid / row_bytes;
+    rows = rows < pn.cnt ? rows : pn.cnt;
+    for (int i = 0; i < (int)rows; ++i) prefetch_l2(n.W[l] + (size_t)(pn.r0 + i) * n.ld[l], (unsigned)row_bytes);
+  };
   // per-CTA slots: partial column sums (+ 8 partial u_j . delta behind them), two buffers
   auto pslot = [&](int buf, int cta) { return A + n.off_panel + ((size_t)buf * kLazyDotSlots + cta) * n.panel_stride; };
 
@@ -440,6 +457,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
         panel_cols_flush(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
       }
       trace(100 + l);
+      prefetch_panel(l - 1);  // streamed next: top-down of layer l-1, or the forward pass of layer 0
       bar.sync_local();
       trace(200 + l);
       // ---- reduce: this rank's partial sums, column slice by column slice.  One rank: the slice
@@ -514,11 +532,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     }
     forward(0, 0, cur ^ 1, m);  // (stages x and synchronises before ubar is read)
     trace(300);
+    prefetch_panel(1);
     bar.sync_all(n, panel(0).cnt > 0);
     trace(400);
     for (int l = 1; l < NL; ++l) {
       forward(l, cur ^ 1, cur ^ 1, m);
       trace(300 + l);
+      prefetch_panel(l + 1 < NL ? l + 1 : last - 1);  // after the last layer: the first wide top-down pass
       bar.sync_all(n, panel(l).cnt > 0);
       trace(400 + l);
     }
@@ -593,6 +613,14 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
     return 1;
   KP p = p_in;
   p.lazy_depth = depth < n.hist_depth ? depth : n.hist_depth;
+  {
+    static const long long prefetch_mb = [] {
+      const char *e = getenv("HPNN_PREFETCH_MB");
+      return e ? atoll(e) : 0LL;  // measured at 4 GPUs: 48 MB costs 3%, so off unless asked for
+    }();
+    // one rank: the barrier is short and a layer is many times L2, nothing to hide behind
+    p.prefetch_bytes = n.world > 1 ? prefetch_mb << 20 : 0;
+  }
   int pmax = 1, rowpart = 8;
   for (int l = 0; l < n.n_layers; ++l) {
     const int pm = panel_max(n.rows[l], grid);

@@ -353,6 +353,7 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
     p.tagged = tagged ? 1 : 0;
   }
   p.lazy_depth = 0;
+  p.prefetch_bytes = 0;
   p.trace = g_trace;
   p.trace_cap = g_trace_cap;
   int max_ld = 8, max_rows = 8;

@@ -79,10 +79,12 @@ class TPBatchRunner:
         out = H.clone()
         if net.type == N.TYPE_SNN:
             ops.softmax_rows_(out, stable_softmax)
-        if mode == "fused":
-            # nobody may start the next forward (and overwrite buffer 0) before everyone has read the result
-            self.epoch += 1
-            N.check(self.lib.hpnn_dev_world_barrier(flags, net.rank, net.world, self.epoch, stream), "hpnn_dev_world_barrier")
+        # Nobody may start the next forward before everyone has read its result: a later "fused" call
+        # stores straight into the peers' buffer 0.  This holds after an "nccl" pass as well (its
+        # last copies into the shared buffers run after the collective has returned on the peers;
+        # seen as a 3e-3 error in one of five 4-GPU runs before the barrier covered both modes).
+        self.epoch += 1
+        N.check(self.lib.hpnn_dev_world_barrier(flags, net.rank, net.world, self.epoch, stream), "hpnn_dev_world_barrier")
         return out
 
     def close(self):
