@@ -25,6 +25,7 @@ NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nv
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp,-Wall,-Wno-unused-function",
           f"-I{ROOT / 'include'}", f"-I{ROOT / 'csrc' / 'core'}", f"-I{ROOT / 'csrc' / 'kernels'}"]
+COMMON += os.environ.get("HPNN_EXTRA_NVCC_FLAGS", "").split()  # experiments, e.g. -DHPNN_W_STREAM
 
 CORE_SOURCES = [
     "csrc/core/io.cpp",
@@ -40,6 +41,7 @@ CORE_SOURCES = [
 ]
 SHIM_SOURCES = ["csrc/capi/libhpnn.cpp"]
 HEADERS = ["include/hpnn_core.h", "csrc/core/kernel_host.hpp", "csrc/kernels/dev_common.cuh", "csrc/kernels/kp_common.cuh",
+           "csrc/kernels/lazy_common.cuh",
            "include/libhpnn.h", "include/libhpnn/common.h", "include/libhpnn/ann.h", "include/libhpnn/snn.h"]
 
 
