@@ -1,6 +1,6 @@
 """Short, single-purpose scenarios for `ncu --set full` (one GPU, few launches).
 
-    python bench/ncu_targets.py kt | kg | kp_wide | kp_snn_stream | kpr_snn | ops_wide"""
+    python bench/ncu_targets.py kt | kg | kp_wide | kpl1_wide | kp_snn_stream | kpr_snn | ops_wide"""
 import os
 import sys
 
@@ -41,8 +41,11 @@ def main():
             for _ in range(4):
                 ops.forward_batch(Wp, cols, X, 0)
         torch.cuda.synchronize()
-    elif which == "kp_wide":
+    elif which == "kp_wide":  # plain streaming trainer
+        os.environ["HPNN_LAZY"] = "0"
         train_case(hp.TYPE_ANN, hp.TRAIN_BP, 784, [8192] * 4, 10, 4)
+    elif which == "kpl1_wide":  # deferred-update row-panel trainer: 16 iterations = two write-back passes
+        train_case(hp.TYPE_ANN, hp.TRAIN_BP, 784, [8192] * 4, 10, 16)
     elif which == "kp_snn_stream":
         os.environ["HPNN_NO_RESIDENT"] = "1"
         train_case(hp.TYPE_SNN, hp.TRAIN_BPM, 784, [1000, 1000], 10, 100)
