@@ -1,25 +1,31 @@
-// K-PL1: deferred-update BP trainer for ONE GPU, organised around row panels.
+// K-PL1: deferred-update BP trainer organised around row panels (one GPU, or a row-split job).
 //
 // Same arithmetic as train_lazy.cu (W_true = S + sum_j u_j (x) v_j, write-back every `depth`
 // iterations; src/ann.c:2281-2467 is the loop being reproduced), different work split: CTA b
-// owns one contiguous panel of rows of every layer for the whole sample, in every phase.
+// owns one contiguous panel of this rank's rows of every layer for the whole sample, in every phase.
 //
-//   forward   : one warp per (row, segment) of the own panel, as in the other trainers.
+//   forward   : wide layers: the CTA streams its panel row by row, every thread holding the x
+//               values of a few column pairs (panel_z_stream); narrow layers: one warp per
+//               (row, segment) as in the other trainers.
 //   top-down  : the CTA streams its panel once, every thread owning a few column pairs:
 //               P_b[c] = sum_{r in panel} W[r,c] delta[r].  No cross-thread reduction, no CTA-wide
 //               barrier inside the pass, every row is read as one contiguous 32 KB run, so this
-//               pass runs at the forward pass's bandwidth (the column tasks of K-P / K-PL reach
-//               ~5.2 TB/s against ~6.3 TB/s because each task ends in a block-wide reduction).
-//               P_b goes to a per-CTA slot in global memory (148 x 64 KB, L2 resident).
+//               pass runs at 6.9 TB/s (the column tasks of K-P / K-PL reach ~5.2 TB/s because each
+//               task ends in a block-wide reduction).  P_b goes to a per-CTA slot in global memory
+//               (148 x 64 KB, L2 resident).
 //   [barrier]
-//   reduce    : CTA b adds the 148 partial vectors for the columns that are ITS rows of the layer
-//               below and turns them into that layer's deltas.  Deltas and the u factors
-//               therefore never leave the CTA: they live in shared memory, the per-CTA staging of
-//               the full delta vector (8192 x 3 loads per CTA and layer) is gone, and the
-//               write-back pass reads its u factors as shared-memory broadcasts.
+//   reduce    : one rank: CTA b adds the 148 partial vectors for the columns that are ITS rows of
+//               the layer below and turns them into that layer's deltas.  Several ranks: the CTA
+//               adds a column slice, sends the sums to the rank owning those rows (peer stores),
+//               and after a cross-rank barrier the owning CTA adds one value per rank.
+//               Either way deltas and u factors never leave the owning CTA: they live in shared
+//               memory, the per-CTA staging of the full delta vector (8192 x 3 loads per CTA and
+//               layer) is gone, and the write-back pass reads its u factors as shared-memory
+//               broadcasts.
 //
 // The v factors (one 8-chunk per column), the partial dot products v_j . x and the partial
-// u_j . delta travel through global memory exactly as in train_lazy.cu.
+// u_j . delta travel through global memory exactly as in train_lazy.cu.  Layer 0 is read-only as
+// well: its input never changes within a sample, so its pending updates are one factor pair.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -288,7 +294,8 @@ __device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, cons
 
 // Row tasks over the own panel.
 //   UPD 0: z_i = S[r,:].x + sum_{j<mcorr} us[i][j] coef[j]   (read-only; us == nullptr: plain)
-//   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                     (immediate update; unused by K-PL1)
+//   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                     (immediate update; kept for layers
+//          that cannot be deferred, not instantiated at present)
 // y goes to every rank's activation buffer (dst); while it is at hand the CTA's share of the next layer's v_j . y (j < m) is formed.
 template <int UPD>
 __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
