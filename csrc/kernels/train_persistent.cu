@@ -233,6 +233,16 @@ long long hpnn_dev_launch_count(int reset) {
   return v;
 }
 
+long long hpnn_abi_sizeof(int which) {
+  switch (which) {
+    case 0: return (long long)sizeof(hpnn_train_result);
+    case 1: return (long long)sizeof(hpnn_train_opts);
+    case 2: return (long long)sizeof(hpnn_conf);
+    case 3: return (long long)sizeof(hpnn_dev_net);
+    default: return -1;
+  }
+}
+
 void hpnn_dev_set_persistent_grid(int ctas) { g_grid_override = ctas; }
 
 void hpnn_dev_set_phase_trace(long long *dev_buf, int capacity_pairs) {

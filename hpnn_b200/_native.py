@@ -106,6 +106,7 @@ def _declare(lib):
         "hpnn_dev_set_persistent_grid": (None, [i]),
         "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),
         "hpnn_dev_set_lazy_panel": (None, [i]),
+        "hpnn_abi_sizeof": (C.c_longlong, [i]),
         "hpnn_dev_set_phase_trace": (None, [vp, i]),
         "hpnn_dev_forward_layer": (i, [vp, i, i, i, vp, vp, i, vp]),
         "hpnn_dev_output_stats": (i, [i, i, vp, vp, i, vp, vp, vp, vp]),
@@ -150,6 +151,12 @@ def load(build_if_missing: bool = True):
             f"native core {_LIB_PATH} is missing: run `python -m hpnn_b200.build` (nvcc, sm_100a)")
     lib = C.CDLL(str(_LIB_PATH), mode=C.RTLD_GLOBAL)
     _declare(lib)
+    # a stale library (older struct layout) must fail here, not corrupt memory later
+    for which, cls in enumerate((TrainResult, TrainOpts, Conf, DevNet)):
+        got = lib.hpnn_abi_sizeof(which)
+        if got != C.sizeof(cls):
+            raise RuntimeError(f"{_LIB_PATH} was built from other sources: sizeof({cls.__name__}) is {got} there, "
+                               f"{C.sizeof(cls)} here; rebuild with `python -m hpnn_b200.build`")
     _lib = lib
     return lib
 

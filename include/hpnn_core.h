@@ -317,6 +317,9 @@ int hpnn_dev_forward_noalloc(int type, int stable_softmax, int n_layers, const i
 
 /* launch counter: number of kernels this library launched since the last reset */
 long long hpnn_dev_launch_count(int reset);
+/* sizeof of the ABI structs as this library was compiled, for bindings that mirror them
+ * (0 hpnn_train_result, 1 hpnn_train_opts, 2 hpnn_conf, 3 hpnn_dev_net; -1 = unknown index) */
+long long hpnn_abi_sizeof(int which);
 
 #ifdef __cplusplus
 }

@@ -145,3 +145,64 @@ def test_dir_walk_skips_dotfiles_and_covers_all(toy_dir):
     files = hp.walk(str(toy_dir / "samples"), 10958)
     assert sorted(os.path.basename(f) for f in files) == sorted(names)
     assert files == hp.walk(str(toy_dir / "samples"), 10958)  # deterministic for a seed
+
+
+def test_arena_layout_regions_are_disjoint_and_cover_the_variants():
+    """hpnn_dev_arena_layout is host code: every region the trainers index must lie inside the arena
+    and overlap no other region, for one rank and for a row-split job, small and wide shapes."""
+    import ctypes as C
+
+    from hpnn_b200 import _native as N
+
+    lib = N.load()
+
+    def layout(dims, rank, world):
+        net = N.DevNet()
+        net.n_layers = len(dims) - 1
+        for i, d in enumerate(dims):
+            net.dims[i] = d
+        net.rank, net.world = rank, world
+        total = lib.hpnn_dev_arena_layout(C.byref(net))
+        assert total > 0 and total == net.arena_doubles
+        return net, total
+
+    def regions(net, total):
+        NL, W = net.n_layers, net.world
+        pad = lambda v: (v + 7) & ~7
+        regs = [("act%d" % i, net.off_act[i], pad(net.dims[i]) * (1 if i == 0 else 4)) for i in range(NL + 1)]
+        regs += [("part%d" % l, net.off_part[l], 2 * W * 4 * net.part_stride[l]) for l in range(NL)]
+        regs += [("target", net.off_target, pad(net.dims[NL])), ("out", net.off_out, pad(net.dims[NL])),
+                 ("flags", net.off_flags, 2 * N.MAX_WORLD)]
+        if net.cta_slots:
+            regs += [("cta%d" % l, net.off_cta_part[l], 2 * net.cta_slots * net.ld[l]) for l in range(1, NL)]
+        if net.hist_depth:
+            for l in range(1, NL):
+                regs += [("hu%d" % l, net.off_hist_u[l], 8 * net.part_stride[l]), ("hv%d" % l, net.off_hist_v[l], 8 * net.ld[l]),
+                         ("hd%d" % l, net.off_hist_dot[l], 8 * W * 160)]
+            if net.panel_stride:
+                regs.append(("panel", net.off_panel, 2 * 160 * net.panel_stride))
+        return regs
+
+    def check(net, total):
+        regs = sorted(regions(net, total), key=lambda r: r[1])
+        for (na, oa, sa), (nb, ob, _) in zip(regs, regs[1:]):
+            assert oa >= 0 and oa + sa <= ob, (na, nb)
+        assert regs[-1][1] + regs[-1][2] <= total
+
+    small, _ = layout([784, 300, 10], 0, 1)
+    assert small.cta_slots > 0 and small.hist_depth == 0 and small.panel_stride == 0
+    check(small, small.arena_doubles)
+    for world in (1, 2, 8):
+        for rank in (0, world - 1):
+            wide, total = layout([784, 8192, 8192, 8192, 8192, 10], rank, world)
+            assert wide.hist_depth == 8 and wide.panel_stride == 8192 + 8 and wide.cta_slots == 0
+            assert wide.rows[1] == 8192 // world and wide.row0[1] == rank * (8192 // world)
+            check(wide, total)
+    # the history threshold is a setting (tests use it to exercise the deferred-update trainers on small nets)
+    lib.hpnn_dev_set_lazy(-1, 0)
+    try:
+        forced, total = layout([40, 600, 300, 12], 0, 1)
+        assert forced.hist_depth == 8 and forced.cta_slots > 0
+        check(forced, total)
+    finally:
+        lib.hpnn_dev_set_lazy(-1, -1)
