@@ -267,7 +267,7 @@ def run_reference(args, cfg):
     env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE",
                                                               "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID")}
     env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(max(1, args.gpus)))
-    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--child", "--gpus", str(args.gpus),
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", args.impl, "--child", "--gpus", str(args.gpus),
            "--steps", str(args.steps), "--warmup", str(args.warmup), "--config", args.config,
            "--ref-streams", str(args.ref_streams)]
     try:
@@ -277,20 +277,23 @@ def run_reference(args, cfg):
             print(lines[-1], flush=True)
         else:
             tail = (r.stderr.strip().splitlines() or r.stdout.strip().splitlines() or ["no output"])[-1]
-            print(json.dumps({"impl": "reference", "n_gpus": args.gpus, "unavailable":
+            print(json.dumps({"impl": args.impl, "n_gpus": args.gpus, "unavailable":
                               ("reference process exited with code %d: %s" % (r.returncode, tail))[:300]}), flush=True)
     except subprocess.TimeoutExpired:
-        print(json.dumps({"impl": "reference", "n_gpus": args.gpus,
+        print(json.dumps({"impl": args.impl, "n_gpus": args.gpus,
                           "unavailable": "reference run exceeded %d s" % args.ref_timeout}), flush=True)
     _set_flag(args)
 
 
 def run_reference_child(args, cfg):
     n_gpus = max(1, args.gpus)
-    out = {"impl": "reference"}
+    out = {"impl": args.impl}
+    shim = args.impl == "shim"  # same host code, but linked against OUR drop-in libhpnn.so (not a reference number)
     try:
         lib_path = os.path.join(ROOT, "baseline", "_ref", "build", "libhpnn_ref_cuda.so")
-        if not os.path.exists(lib_path):
+        if shim:
+            lib_path = os.path.join(ROOT, "hpnn_b200", "lib", "libhpnn.so")
+        elif not os.path.exists(lib_path):
             sys.path.insert(0, os.path.join(ROOT, "baseline"))
             import build_ref
             build_ref.build(("cuda",))
@@ -354,8 +357,10 @@ def run_reference_child(args, cfg):
             "data": "synthetic (same files, seed and visiting order as the ours arm)",
             "config": {"model": "%s %s" % (typ, "-".join(str(d) for d in [n_in, *hid, n_out])), "name": args.config,
                        "baseline_config": desc, "global_batch": 1, "seq_len": None,
-                       "parallelism": "reference row split over %d GPU(s) x %d stream(s), one process" % (n_gpus, args.ref_streams),
-                       "build": "unmodified sources, -D_OMP -D_CUDA -D_CUBLAS, nvcc sm_100 (baseline/build_ref.py)",
+                       "parallelism": ("hpnn-b200 through the libhpnn C API, row split over %d GPU(s), one process" % n_gpus) if shim else
+                       "reference row split over %d GPU(s) x %d stream(s), one process" % (n_gpus, args.ref_streams),
+                       "build": "hpnn_b200/lib/libhpnn.so (drop-in shim over the sm_100a engine)" if shim else
+                       "unmodified sources, -D_OMP -D_CUDA -D_CUBLAS, nvcc sm_100 (baseline/build_ref.py)",
                        "iterations_timed": sum(iters), "iterations_per_s": sum(iters) / (ms * 1e-3),
                        "samples_converged": len(re.findall(r"SUCCESS", text))},
             "clocks": clk,
@@ -365,7 +370,7 @@ def run_reference_child(args, cfg):
         })
         shutil.rmtree(tmp, ignore_errors=True)
     except Exception as e:  # the contract: report and exit 0
-        out = {"impl": "reference", "unavailable": ("%s: %s" % (type(e).__name__, e)).replace("\n", " ")[:300]}
+        out = {"impl": args.impl, "unavailable": ("%s: %s" % (type(e).__name__, e)).replace("\n", " ")[:300]}
     print(json.dumps(out), flush=True)
 
 
@@ -396,7 +401,9 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "shim"],
+                    help="ours: the framework's own API; reference: unmodified reference build; shim: the reference "
+                         "arm's host code (nn_load_conf + nn_train_kernel) linked against our drop-in libhpnn.so")
     ap.add_argument("--config", default=os.environ.get("HPNN_BENCH_CONFIG", "wide_ann"), choices=sorted(CONFIGS))
     ap.add_argument("--ref-streams", type=int, default=1)
     ap.add_argument("--ref-timeout", type=int, default=3000)
@@ -404,7 +411,7 @@ def main():
     args = ap.parse_args()
     args.warmup = max(3, args.warmup)
     cfg = CONFIGS[args.config]
-    if args.impl == "reference":
+    if args.impl in ("reference", "shim"):
         (run_reference_child if args.child else run_reference)(args, cfg)
     else:
         run_ours(args, cfg)
