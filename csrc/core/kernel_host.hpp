@@ -11,6 +11,9 @@ struct hpnn_kernel {
   // CPU-engine work space (lazily sized)
   std::vector<std::vector<double>> act;  // act[0]=input, act[l+1]=output of layer l
   std::vector<std::vector<double>> delta;
+  std::vector<std::vector<double>> hold;  // activations of the previous sweep (CPU engine, fused update+forward)
   std::vector<std::vector<double>> dW;   // momentum
+  // CPU engine, per-sample training loop: weights / momenta with 8 rows interleaved per column
+  std::vector<std::vector<double>> packW, packM;
   int n_layers() const { return (int)dims.size() - 1; }
 };
