@@ -84,6 +84,12 @@ def _declare(lib):
         "hpnn_train_opts_default": (None, [C.POINTER(TrainOpts), i, i, i]),
         "hpnn_set_omp_threads": (None, [i]),
         "hpnn_cpu_forward": (i, [vp, i, i, dp, dp]),
+        "hpnn_cpu_act": (dp, [vp, i]),
+        "hpnn_cpu_momentum_init": (None, [vp]),
+        "hpnn_cpu_momentum_zero": (None, [vp]),
+        "hpnn_cpu_forward_inplace": (i, [vp, i, i]),
+        "hpnn_cpu_error": (C.c_double, [vp, i, dp]),
+        "hpnn_cpu_train_iteration": (C.c_double, [vp, C.POINTER(TrainOpts), dp]),
         "hpnn_cpu_train_sample": (i, [vp, C.POINTER(TrainOpts), dp, dp, C.POINTER(TrainResult), dp]),
         "hpnn_dev_arena_layout": (ll, [C.POINTER(DevNet)]),
         "hpnn_cuda_device_count": (i, []),

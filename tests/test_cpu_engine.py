@@ -84,3 +84,46 @@ def test_loop_bounds_min_and_max_iter():
     e2 = CpuEngine(k, N.TYPE_ANN, N.TRAIN_BP, delta=1e9, min_iter=40)
     r2 = e2.train(X[0], T[0])
     assert r2.n_iter >= 41  # at least MIN+1 iterations even when dE is already small
+
+
+@pytest.mark.parametrize("threads", [1, 3])
+@pytest.mark.parametrize("nn_type,train", [(N.TYPE_ANN, N.TRAIN_BP), (N.TYPE_ANN, N.TRAIN_BPM), (N.TYPE_SNN, N.TRAIN_BP),
+                                           (N.TYPE_SNN, N.TRAIN_BPM)])
+def test_packed_sample_loop_equals_single_step_path_bitwise(nn_type, train, threads):
+    """hpnn_cpu_train_sample runs on weights packed 8 rows per column with the update fused into
+    the forward pass; the single-step entry points (what ann_kernel_train / snn_kernel_train of the
+    C API call) keep the plain row-major loops.  Same operations in the same order per row, so after
+    the same number of iterations every weight must be equal to the last bit -- for row counts that
+    are not multiples of 8, layers wide enough for a thread team and several hidden layers."""
+    import ctypes as C
+    lib = N.load()
+    dp = C.POINTER(C.c_double)
+    lib.hpnn_set_omp_threads(threads)
+    try:
+        for n_in, hid, n_out in [(13, [9, 7], 3), (70, [300, 41], 10), (5, [8], 8)]:
+            k, _ = hp.generate_kernel(321, n_in, hid, n_out)
+            rng = np.random.default_rng(7)
+            x = rng.random(n_in)
+            t = np.full(n_out, 0.0 if nn_type == N.TYPE_SNN else -1.0)
+            t[1] = 1.0
+            n_it = 23
+            a = CpuEngine(k, nn_type, train, max_iter=n_it - 1, min_iter=n_it + 5, delta=1e-300)
+            assert a.train(x, t).n_iter == n_it
+            b = CpuEngine(k, nn_type, train)
+            if train == N.TRAIN_BPM:
+                lib.hpnn_cpu_momentum_init(b.h)
+                lib.hpnn_cpu_momentum_zero(b.h)
+            inp = lib.hpnn_cpu_act(b.h, 0)
+            for i in range(n_in):
+                inp[i] = x[i]
+            lib.hpnn_cpu_forward_inplace(b.h, nn_type, 0)
+            tt = np.ascontiguousarray(t)
+            for _ in range(n_it):
+                lib.hpnn_cpu_train_iteration(b.h, C.byref(b.opts), tt.ctypes.data_as(dp))
+            for wa, wb in zip(a.kernel().weights, b.kernel().weights):
+                assert np.array_equal(wa, wb)
+            assert np.array_equal(a.run(x), b.run(x))
+            a.close()
+            b.close()
+    finally:
+        lib.hpnn_set_omp_threads(0)
