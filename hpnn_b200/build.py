@@ -71,7 +71,11 @@ def _compile(src, verbose, ptxas_v=False):
         return None
     OBJDIR.mkdir(parents=True, exist_ok=True)
     tag = _digest([src] + HEADERS, extra=" ".join(COMMON + ARCH))
-    obj = OBJDIR / (src.replace("/", "_") + f".{tag}.o")
+    stem = src.replace("/", "_")
+    obj = OBJDIR / f"{stem}.{tag}.o"
+    for old in OBJDIR.glob(f"{stem}.*.o"):  # objects of earlier versions of this source
+        if old != obj:
+            old.unlink()
     if obj.exists():
         return obj
     cmd = [NVCC, *ARCH, *COMMON, "-c", src_path, "-o", obj]
