@@ -73,6 +73,7 @@ struct DotOut {
   int n;
   const double *HV;  // factor chunks of the next layer, indexed by the global row of this layer
   int row0;
+  unsigned long long tag;  // != 0: publish the chunk as 8 {value, tag} pairs (tagged hand-over)
 };
 
 

@@ -131,12 +131,15 @@ __device__ __forceinline__ void panel_cols_read(const double *W, int ld, Panel p
 // the thread's column pair stay in registers for the whole panel):
 //   P[c] from the OLD stored weights, then w += sum_{j<m} us[i][j] v_j[c] + (lr*d_i) h[c].
 // Pout == nullptr: final write-back, no sums wanted.
+template <bool HS>  // HS: h lives in shared memory
 __device__ __forceinline__ void panel_cols_flush(double *W, int ld, Panel pn, const double *dsl, const double *us,
                                                  const double *HV, const double *h, double lr, int m, double *Pout) {
   const double2 zero2 = make_double2(0.0, 0.0);
   const int mc = (m + 1) >> 1;
   for (int c = 2 * threadIdx.x; c < ld; c += kPanelCols) {
-    const double h0 = ldg_cg(h + c), h1 = ldg_cg(h + c + 1);
+    // (lr == 0: final write-back, h is not wanted and may be in another format)
+    const double h0 = lr == 0.0 ? 0.0 : (HS ? h[c] : ldg_cg(h + c));
+    const double h1 = lr == 0.0 ? 0.0 : (HS ? h[c + 1] : ldg_cg(h + c + 1));
     double v0[kLazyChunk], v1[kLazyChunk];
     {
       const double2 *a = reinterpret_cast<const double2 *>(HV + (size_t)c * kLazyChunk);
@@ -341,10 +344,47 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
     __shared__ double mine_dots[kLazyChunk];
     chunk_block_sum(acc, m, mine_dots, red);
     if (threadIdx.x < kLazyChunk)
-      for (int q = 0; q < dots.n; ++q) stg_cg(dots.p[q] + threadIdx.x, mine_dots[threadIdx.x]);
+      for (int q = 0; q < dots.n; ++q) {
+        if (dots.tag) st_pair<true>(dots.p[q], threadIdx.x, mine_dots[threadIdx.x], dots.tag);
+        else stg_cg(dots.p[q] + threadIdx.x, mine_dots[threadIdx.x]);
+      }
   }
 }
 
+// tagged variant of gather_dots: every producer chunk is 8 {value, tag} pairs in this rank's arena,
+// polled until the tag of the running iteration shows up (no barrier, no fence)
+__device__ __forceinline__ void gather_dots_tagged(const hpnn_dev_net &n, int l, int m, unsigned long long tag,
+                                                   double *coef, double *red) {
+  const double *slots = n.arena[n.rank] + n.off_hist_dot[l];
+  const int N = n.dims[l];  // rows of layer l-1, split over the ranks
+  double acc[kLazyChunk];
+#pragma unroll
+  for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
+  for (int idx = threadIdx.x; idx < n.world * kLazyDotSlots; idx += kThreads) {
+    const int q = idx / kLazyDotSlots, b = idx % kLazyDotSlots;
+    const int rows_q = row0_of(q + 1, N, n.world) - row0_of(q, N, n.world);
+    if (b < (int)gridDim.x && b < rows_q) {
+      const double *addr[kLazyChunk];
+      bool want[kLazyChunk];
+      double v[kLazyChunk];
+#pragma unroll
+      for (int j = 0; j < kLazyChunk; ++j) {
+        want[j] = j < m;
+        addr[j] = slots + 2 * ((size_t)idx * kLazyChunk + j);
+      }
+      ld_pairs_wait<kLazyChunk, false>(addr, want, tag, v);
+#pragma unroll
+      for (int j = 0; j < kLazyChunk; ++j) acc[j] += v[j];
+    }
+  }
+  chunk_block_sum(acc, m, coef, red);
+}
+
+// TG: several ranks with the tagged-pair hand-over of K-P (kp_common.cuh): activations, slice sums
+// and dot-product chunks cross NVLink as {value, tag} pairs and are polled by their consumers, the
+// grid barriers stay local to the GPU and there is no system-scope fence.  TG == false: plain
+// buffers + fence / flag barriers (also the single-rank case).
+template <bool TG>
 __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid_constant__ KP p) {
   extern __shared__ double smem[];
   const hpnn_dev_net &n = p.net;
@@ -363,6 +403,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   const bool snn = p.type == HPNN_TYPE_SNN;
   const int depth = p.lazy_depth;
   const bool multi = n.world > 1;
+  constexpr bool tg = TG;
+  const unsigned long long launch = (unsigned long long)ld_relaxed_gpu(n.local_sync + 160) + 1ull;
+  auto tag_of = [&](int iteration) { return (launch << 32) | (unsigned long long)(unsigned)iteration; };
 
   Barrier bar;
   bar.init(n);
@@ -376,9 +419,18 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   };
   int cur = 0;
   auto act_peer = [&](int q, int i, int buf) -> double * {
-    return n.arena[q] + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]));
+    return n.arena[q] + n.off_act[i] + ((i == 0) ? 0 : (size_t)buf * pad8(n.dims[i]) * (tg ? 2 : 1));
   };
   auto act_of = [&](int i, int buf) -> double * { return act_peer(n.rank, i, buf); };
+  // act[i] (buffer buf) into shared memory; tagged mode: wait until every value carries `tag`
+  auto stage_act = [&](double *dst_smem, int i, int buf, unsigned long long tag) {
+    if (tg && i > 0) stage_pairs<false>(dst_smem, act_of(i, buf), n.dims[i], pad8(n.dims[i]), tag);
+    else stage_vec(dst_smem, act_of(i, buf), pad8(n.dims[i]));
+  };
+  auto phase_sync = [&](bool remote) {
+    if (tg) bar.sync_local();
+    else bar.sync_all(n, remote);
+  };
   auto panel = [&](int l) { return panel_of(n.rows[l], grid, b); };  // local row indices of this rank's block
   auto us_of = [&](int l) { return us + (size_t)l * pmax * kLazyChunk; };
   // first rows of the own panel of layer l into L2, at most p.prefetch_bytes per rank and call
@@ -409,20 +461,25 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     for (int i = threadIdx.x; i < pmax; i += kThreads) us[(size_t)i * kLazyChunk] = 0.0;
     __syncthreads();
   }
-  auto forward = [&](int l, int src_buf, int dst_buf, int m) {
-    stage_vec(xs, act_of(l, src_buf), pad8(n.dims[l]));
+  auto forward = [&](int l, int src_buf, int dst_buf, int m, unsigned long long tag) {
+    stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
     __syncthreads();
-    if (l >= 1 && m > 0) gather_dots(n, l, m, coef, red);  // coef[j] = v_j . x
+    if (l >= 1 && m > 0) {  // coef[j] = v_j . x
+      if (tg) gather_dots_tagged(n, l, m, tag, coef, red);
+      else gather_dots(n, l, m, coef, red);
+    }
     Dst dst;  // all-gather by peer stores
     dst.n = n.world;
-    dst.tag = 0ull;
-    for (int q = 0; q < n.world; ++q) dst.p[q] = act_peer(q, l + 1, dst_buf) + (size_t)n.row0[l];
+    dst.tag = tg ? tag : 0ull;
+    for (int q = 0; q < n.world; ++q) dst.p[q] = act_peer(q, l + 1, dst_buf) + (size_t)n.row0[l] * (tg ? 2 : 1);
     DotOut dots;
     dots.n = n.world;
+    dots.tag = tg ? tag : 0ull;
     dots.p[0] = nullptr;
     if (l + 1 < NL && m > 0) {
       for (int q = 0; q < n.world; ++q)
-        dots.p[q] = n.arena[q] + n.off_hist_dot[l + 1] + (size_t)(n.rank * kLazyDotSlots + b) * kLazyChunk;
+        dots.p[q] = n.arena[q] + n.off_hist_dot[l + 1] +
+                    (size_t)(n.rank * kLazyDotSlots + b) * kLazyChunk * (tg ? 2 : 1);
       dots.HV = A + n.off_hist_v[l + 1];
       dots.row0 = n.row0[l];
     }
@@ -433,14 +490,24 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   };
 
   for (int l = 0; l < NL; ++l) {
-    forward(l, cur, cur, 0);
-    bar.sync_all(n, panel(l).cnt > 0);
+    forward(l, cur, cur, 0, tag_of(0));
+    phase_sync(panel(l).cnt > 0);
   }
   const double *target = A + n.off_target;
   const int last = NL - 1;
   const Panel plast = panel(last);
   const int out_row0 = n.row0[last] + plast.r0;
-  OutStats st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, out_row0, plast.cnt, dsl, nullptr, red);
+  // output statistics from the gathered output vector (tagged mode: gathered into xs first)
+  auto evaluate = [&](unsigned long long tag, int row0, int rows, double *dsp, double *o_out) -> OutStats {
+    if (tg) {
+      __syncthreads();
+      stage_act(xs, NL, cur, tag);
+      __syncthreads();
+      return output_stats<true>(p.type, p.stable, xs, target, n_out, row0, rows, dsp, o_out, red);
+    }
+    return output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, row0, rows, dsp, o_out, red);
+  };
+  OutStats st = evaluate(tag_of(0), out_row0, plast.cnt, dsl, nullptr);
   double E = st.err;
   const double init_err = E;
   int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
@@ -450,13 +517,19 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   for (;;) {
     ++iter;
     trace(1);
+    const unsigned long long tag = tag_of(iter);
     const bool flush = (m + 1 >= depth);
     // ---- top-down
     for (int l = last; l >= 1; --l) {
       const Panel pn = panel(l);
       double *ul = us_of(l);
       double *HV = A + n.off_hist_v[l];
-      const double *h = act_of(l, cur);
+      const double *h = act_of(l, cur);  // input of layer l in the previous sweep
+      if (tg) {  // present for a whole sweep already, but stored as pairs: unpack into shared memory
+        stage_act(xs, l, cur, tag - 1);
+        __syncthreads();
+        h = xs;
+      }
       double *Pout = pslot(l & 1, b);
       if (pn.cnt > 0 && threadIdx.x < 32) {
         // this panel's share of u_j . delta (factor j = lane & 7, rows dealt to the four lane groups),
@@ -472,10 +545,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
       if (!flush) {
         for (int i = threadIdx.x; i < pn.cnt; i += kThreads) ul[(size_t)i * kLazyChunk + m] = p.lr * dsl[i];
         const int gt = b * kThreads + threadIdx.x;
-        for (int c = gt; c < n.ld[l]; c += grid * kThreads) stg_cg(HV + (size_t)c * kLazyChunk + m, ldg_cg(h + c));
+        for (int c = gt; c < n.ld[l]; c += grid * kThreads)
+          stg_cg(HV + (size_t)c * kLazyChunk + m, tg ? h[c] : ldg_cg(h + c));
         if (pn.cnt > 0) panel_cols_read(n.W[l], n.ld[l], pn, dsl, Pout);
       } else if (pn.cnt > 0) {
-        panel_cols_flush(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
+        panel_cols_flush<TG>(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
       }
       trace(100 + l);
       prefetch_panel(l - 1);  // streamed next: top-down of layer l-1, or the forward pass of layer 0
@@ -496,7 +570,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
         chunk_block_sum(acc, m, coef, red);  // coef[j] = u_j . delta_l over this rank's rows
       }
       const Panel slice = panel_of(n.dims[l], grid, b);  // columns of layer l == rows of layer l-1 (global)
-      const double *hb = act_of(l, cur);                   // output of layer l-1
+      const double *hb = h;                   // output of layer l-1
       const int cols = n.dims[l];
       for (int ci0 = 0; ci0 < slice.cnt; ci0 += 64) {
         const int ci = ci0 + (threadIdx.x & 63), g = threadIdx.x >> 6;
@@ -526,21 +600,37 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
             dsl[ci] = pc * dact_f(ldg_cg(hb + c));
           } else {
             const int own = owner_of_row(c, cols, n.world);
-            stg_cg(n.arena[own] + n.off_part[l - 1] + (size_t)(n.rank * kMaxRsplit) * n.part_stride[l - 1] +
-                       (c - row0_of(own, cols, n.world)),
-                   pc);
+            const size_t slot = (size_t)(n.rank * kMaxRsplit) * n.part_stride[l - 1] + (c - row0_of(own, cols, n.world));
+            if (tg) st_pair<true>(n.arena[own] + n.off_part[l - 1], (long long)slot, pc, tag);
+            else stg_cg(n.arena[own] + n.off_part[l - 1] + slot, pc);
           }
         }
       }
       if (multi) {
-        bar.sync_all(n, slice.cnt > 0);
+        if (!tg) bar.sync_all(n, slice.cnt > 0);
         trace(500 + l);
         const Panel below = panel(l - 1);
         const double *part = A + n.off_part[l - 1];
         for (int i = threadIdx.x; i < below.cnt; i += kThreads) {
           double s = 0.0;
-          for (int g = 0; g < n.world; ++g) s += ldg_cg(part + (size_t)(g * kMaxRsplit) * n.part_stride[l - 1] + below.r0 + i);
-          dsl[i] = s * dact_f(ldg_cg(hb + n.row0[l - 1] + below.r0 + i));
+          if (tg) {  // one {value, tag} pair per rank, polled until this iteration's value is there
+            const double *addr[HPNN_MAX_WORLD];
+            bool want[HPNN_MAX_WORLD];
+            double v[HPNN_MAX_WORLD];
+#pragma unroll
+            for (int g = 0; g < HPNN_MAX_WORLD; ++g) {
+              want[g] = g < n.world;
+              addr[g] = part + 2 * ((size_t)((want[g] ? g : 0) * kMaxRsplit) * n.part_stride[l - 1] + below.r0 + i);
+            }
+            ld_pairs_wait<HPNN_MAX_WORLD, false>(addr, want, tag, v);
+#pragma unroll
+            for (int g = 0; g < HPNN_MAX_WORLD; ++g) s += v[g];
+            dsl[i] = s * dact_f(hb[n.row0[l - 1] + below.r0 + i]);  // hb == xs here
+          } else {
+            for (int g = 0; g < n.world; ++g)
+              s += ldg_cg(part + (size_t)(g * kMaxRsplit) * n.part_stride[l - 1] + below.r0 + i);
+            dsl[i] = s * dact_f(ldg_cg(hb + n.row0[l - 1] + below.r0 + i));
+          }
         }
       }
       __syncthreads();
@@ -551,20 +641,20 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
       const Panel p0 = panel(0);
       for (int i = threadIdx.x; i < p0.cnt; i += kThreads) us[(size_t)i * kLazyChunk] += p.lr * dsl[i];  // ubar
     }
-    forward(0, 0, cur ^ 1, m);  // (stages x and synchronises before ubar is read)
+    forward(0, 0, cur ^ 1, m, tag);  // (stages x and synchronises before ubar is read)
     trace(300);
     prefetch_panel(1);
-    bar.sync_all(n, panel(0).cnt > 0);
+    phase_sync(panel(0).cnt > 0);
     trace(400);
     for (int l = 1; l < NL; ++l) {
-      forward(l, cur ^ 1, cur ^ 1, m);
+      forward(l, cur ^ 1, cur ^ 1, m, tag);
       trace(300 + l);
       prefetch_panel(l + 1 < NL ? l + 1 : last - 1);  // after the last layer: the first wide top-down pass
-      bar.sync_all(n, panel(l).cnt > 0);
+      phase_sync(panel(l).cnt > 0);
       trace(400 + l);
     }
     cur ^= 1;
-    st = output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, out_row0, plast.cnt, dsl, nullptr, red);
+    st = evaluate(tag, out_row0, plast.cnt, dsl, nullptr);
     trace(2);
     dE = E - st.err;
     E = st.err;
@@ -599,12 +689,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     for (int l = 1; l < NL; ++l) {
       const Panel pn = panel(l);
       if (pn.cnt > 0)
-        panel_cols_flush(n.W[l], n.ld[l], pn, dsl, us_of(l), A + n.off_hist_v[l], act_of(l, cur), 0.0, m, nullptr);
+        panel_cols_flush<false>(n.W[l], n.ld[l], pn, dsl, us_of(l), A + n.off_hist_v[l], act_of(l, cur), 0.0, m, nullptr);
     }
   }
-  if (b == 0) output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, 0, 0, nullptr, A + n.off_out, red);
+  if (b == 0) evaluate(tag_of(iter), 0, 0, nullptr, A + n.off_out);  // publish the final (normalised) output
   bar.finish();
-  if (b == 0 && threadIdx.x == 0) n.local_sync[160] = ld_relaxed_gpu(n.local_sync + 160) + 1u;
+  if (b == 0 && threadIdx.x == 0) n.local_sync[160] = (unsigned)launch;
   if (b == 0 && threadIdx.x == 0 && p.result) {
     hpnn_train_result r;
     r.init_err = init_err;
@@ -629,7 +719,7 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
   const int disabled = g_lazy_panel >= 0 ? !g_lazy_panel : disabled_env;
   const int depth = lazy_depth_setting();
   const hpnn_dev_net &n = p_in.net;
-  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || p_in.train != HPNN_TRAIN_BP || p_in.tagged ||
+  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || p_in.train != HPNN_TRAIN_BP ||
       n.hist_depth < 2 || n.panel_stride <= 0 || n.n_layers < 2)
     return 1;
   KP p = p_in;
@@ -652,13 +742,14 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
   p.max_rows = pmax;  // the kernel's carve-up uses the panel height, not the layer height
   const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart);
   if (smem > 227 * 1024) return 1;
-  cudaError_t e = cudaFuncSetAttribute((const void *)k_train_sample_lazy1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const void *kfn = p.tagged ? (const void *)k_train_sample_lazy1<true> : (const void *)k_train_sample_lazy1<false>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) {
     set_error("cudaFuncSetAttribute(k_train_sample_lazy1)", e);
     return -1;
   }
   void *args[] = {(void *)&p};
-  e = cudaLaunchCooperativeKernel((const void *)k_train_sample_lazy1, dim3(grid), dim3(kThreads), args, smem,
+  e = cudaLaunchCooperativeKernel(kfn, dim3(grid), dim3(kThreads), args, smem,
                                   (cudaStream_t)stream);
   if (e != cudaSuccess) {
     set_error("cudaLaunchCooperativeKernel(k_train_sample_lazy1)", e);

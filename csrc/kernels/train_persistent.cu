@@ -316,7 +316,7 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
         net->off_hist_v[l] = off;
         off += (long long)kLazyChunk * net->ld[l];
         net->off_hist_dot[l] = off;
-        off += (long long)kLazyChunk * W * kLazyDotSlots;
+        off += 2LL * kLazyChunk * W * kLazyDotSlots;  // may hold {value, tag} pairs
       }
     }
   }

@@ -79,8 +79,11 @@ def main():
     lib = N.load()
     os.environ["HPNN_TP_PROTOCOL"] = "barrier"  # the variant uses the fence + flag barrier protocol
     lib.hpnn_dev_set_lazy(8, 0)
-    for panel in (1, 0):  # row panels (train_lazy1.cu) / column tasks (train_lazy.cu)
+    # (panel, protocol): row panels (train_lazy1.cu) with fence + flag barriers or tagged pairs,
+    # column tasks (train_lazy.cu, barrier protocol only)
+    for panel, proto in ((1, "barrier"), (1, "tagged"), (0, "barrier")):
         lib.hpnn_dev_set_lazy_panel(panel)
+        os.environ["HPNN_TP_PROTOCOL"] = proto
         for nn_type in (N.TYPE_ANN, N.TYPE_SNN):
             k, _ = hp.generate_kernel(31, 72, [520, 264, 130], 10)
             X, T = problem(nn_type, 72, 10, 2, 17)
@@ -98,7 +101,7 @@ def main():
                 kl = lazy.kernel()
                 if rank == 0:
                     e_w = max(float(np.abs(a - b).max()) for a, b in zip(kl.weights, cpu.kernel().weights))
-                    print(f"case deferred-update panel={panel} type={nn_type} iters={n_it} world={world}: "
+                    print(f"case deferred-update panel={panel} {proto} type={nn_type} iters={n_it} world={world}: "
                           f"max|dW|={e_w:.2e} max|dE|={e_err:.2e}", flush=True)
                     if not (e_w < 1e-11 and e_err < 1e-11):
                         fails += 1

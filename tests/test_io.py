@@ -178,7 +178,7 @@ def test_arena_layout_regions_are_disjoint_and_cover_the_variants():
         if net.hist_depth:
             for l in range(1, NL):
                 regs += [("hu%d" % l, net.off_hist_u[l], 8 * net.part_stride[l]), ("hv%d" % l, net.off_hist_v[l], 8 * net.ld[l]),
-                         ("hd%d" % l, net.off_hist_dot[l], 8 * W * 160)]
+                         ("hd%d" % l, net.off_hist_dot[l], 2 * 8 * W * 160)]
             if net.panel_stride:
                 regs.append(("panel", net.off_panel, 2 * 160 * net.panel_stride))
         return regs
