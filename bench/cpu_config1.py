@@ -24,8 +24,9 @@ def run(cmd, cwd, env=None):
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 6
     threads = sys.argv[2] if len(sys.argv) > 2 else "4"
+    config = sys.argv[3] if len(sys.argv) > 3 else "ann_mnist"  # any bench.py config; config 1 is ann_mnist
     tmp = tempfile.mkdtemp(prefix="hpnn_cfg1_")
-    conf = bench.make_dataset(bench.CONFIGS["ann_mnist"], n, 1, tmp)
+    conf = bench.make_dataset(bench.CONFIGS[config], n, 1, tmp)
     env = dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS=threads)
     out = []
     ref = os.path.join(ROOT, "baseline", "_ref", "build", "train_nn_cpu")
