@@ -144,3 +144,64 @@ def train_sample(weights: List[torch.Tensor], x: torch.Tensor, t: torch.Tensor, 
             break
     res.n_iter, res.final_de, res.last_err, res.success = it, dE, E, ok
     return res, acts[-1]
+
+
+def train_iterations_deferred(weights: List[torch.Tensor], x: torch.Tensor, t: torch.Tensor, nn_type: int, lr: float,
+                              iterations: int, depth: int = 8, stable: bool = False) -> List[torch.Tensor]:
+    """Plain PyTorch restatement of the deferred-update BP trainers (csrc/kernels/train_lazy.cu,
+    train_lazy1.cu): ``iterations`` BP iterations on one sample, updating ``weights`` in place.
+
+    Layer l >= 1 keeps its last m < ``depth`` rank-1 updates as factors ``u_j = lr*delta_l``,
+    ``v_j = h_(l-1)`` instead of adding them to the stored matrix S:
+
+        W_true^T d = S^T d + sum_j v_j (u_j . d)        W_true x = S x + sum_j u_j (v_j . x)
+
+    and S is brought up to date every ``depth`` iterations (and at the end).  Layer 0 always sees
+    the same input, so its updates collapse into one factor pair ``S0 + ubar (x) x``.  Returns the
+    activations of the last forward pass.  Equal to ``apply_update`` after every iteration up to
+    the rounding of the two correction sums (tests/test_deferred_reference.py)."""
+    L = len(weights)
+    U: List[List[torch.Tensor]] = [[] for _ in range(L)]  # pending factors per layer (l >= 1)
+    V: List[List[torch.Tensor]] = [[] for _ in range(L)]
+    ubar = torch.zeros(weights[0].shape[0], dtype=weights[0].dtype, device=weights[0].device)
+    xx = x @ x
+
+    def fwd() -> List[torch.Tensor]:
+        acts = [x]
+        for l, S in enumerate(weights):
+            h = acts[-1]
+            z = S @ h
+            if l == 0:
+                z = z + ubar * xx
+            else:
+                for u, v in zip(U[l], V[l]):
+                    z = z + u * (v @ h)
+            acts.append(softmax_ref(z, stable) if (l == L - 1 and nn_type == TYPE_SNN) else act(z))
+        return acts
+
+    def flush(l: int) -> None:
+        for u, v in zip(U[l], V[l]):  # oldest first, like the immediate updates
+            weights[l] += torch.outer(u, v)
+        U[l].clear()
+        V[l].clear()
+
+    acts = fwd()
+    for _ in range(iterations):
+        d = [None] * L
+        d[L - 1] = output_delta(acts[L], t, nn_type)
+        for l in range(L - 1, 0, -1):
+            p = weights[l].T @ d[l]
+            for u, v in zip(U[l], V[l]):
+                p = p + v * (u @ d[l])
+            d[l - 1] = p * dact(acts[l])
+        for l in range(1, L):
+            U[l].append(lr * d[l])
+            V[l].append(acts[l].clone())
+            if len(U[l]) >= depth:
+                flush(l)
+        ubar += lr * d[0]
+        acts = fwd()
+    for l in range(1, L):
+        flush(l)
+    weights[0] += torch.outer(ubar, x)
+    return acts
