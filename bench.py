@@ -54,12 +54,24 @@ def rank_world():
 
 
 # ----------------------------------------------------------------------------- data
+def write_sample_text(path, x, t, comment):
+    """Sample file in the reference's text format (src/libhpnn.c:1088-1136; the writers are
+    tutorials/mnist/prepare_mnist.c:47-60).  Plain Python on purpose: both arms of the benchmark
+    create their data with this function, and the reference arm must not map any of this
+    repository's native code (byte-identical to hpnn_sample_write, tests/test_bench_contract.py)."""
+    with open(path, "w") as f:
+        f.write("[input] %i\n" % len(x))
+        f.write(" ".join("%7.5f" % v for v in x))
+        f.write("\n[output] %i  #%s\n" % (len(t), comment))
+        f.write(" ".join("%.1f" % v for v in t))
+        f.write("\n")
+
+
 def make_dataset(cfg, n_warm, n_timed, root):
     """Synthetic samples of the config's shape in two directories (+ nn.conf)."""
     import numpy as np
 
-    from hpnn_b200.samples import write_sample
-
+    write_sample = write_sample_text
     typ, train, n_in, hid, n_out, _ = cfg
     rng = np.random.default_rng(2024)
     lo = 0.0 if typ == "SNN" else -1.0
@@ -78,6 +90,22 @@ def make_dataset(cfg, n_warm, n_timed, root):
                 f"[hidden] {' '.join(str(h) for h in hid)}\n[output] {n_out}\n[train] {train}\n"
                 f"[sample_dir] {root}/warm\n[test_dir] {root}/timed\n")
     return conf
+
+
+def config_block(args, cfg, n_gpus):
+    """The ``config`` object of the JSON line: key for key and value for value the same in both
+    arms (everything arm-specific or measured goes to ``detail``)."""
+    typ, train, n_in, hid, n_out, desc = cfg
+    wmb = sum(a * b for a, b in zip([n_in, *hid], [*hid, n_out])) * 8 / 1e6
+    return {"model": "%s %s" % (typ, "-".join(str(d) for d in [n_in, *hid, n_out])), "name": args.config,
+            "baseline_config": desc, "global_batch": 1, "seq_len": None,
+            "parallelism": "tp%d (row split of every layer over %d GPU(s))" % (n_gpus, n_gpus),
+            "l2": "weights %.0f MB per pass (L2 is 126 MB); the ours arm also writes 256 MiB between timed steps, "
+                  "the reference's directory loop cannot be interrupted" % wmb}
+
+
+def metric_name(cfg):
+    return "train_nn samples/s (per-sample convergent %s training, fp64)" % cfg[1]
 
 
 class ClockSampler:
@@ -229,19 +257,17 @@ def run_ours(args, cfg):
     K = len(timed)
     if rank == 0:
         out = {
-            "metric": "train_nn samples/s (per-sample convergent %s training, fp64)" % train,
+            "metric": metric_name(cfg),
             "value": K / (dev_ms * 1e-3), "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": len(warm),
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "fp64", "data": "synthetic (uniform [0,1) inputs, one-hot targets), random-init weights "
                                       "(glibc random(), seed %d)" % SEED,
             "impl": "ours",
-            "config": {"model": "%s %s" % (typ, "-".join(str(d) for d in [n_in, *hid, n_out])), "name": args.config,
-                       "baseline_config": desc, "global_batch": 1, "seq_len": None,
-                       "parallelism": "tp%d (row split of every layer)" % world,
-                       "l2": "flushed between timed steps (256 MiB write)" + (
-                           "; weights %.0f MB > L2" % (sum(a * b for a, b in zip([n_in, *hid], [*hid, n_out])) * 8 / 1e6)),
-                       "iterations_timed": iters_dev, "iterations_per_s": iters_dev / (dev_ms * 1e-3),
-                       "samples_converged": n_ok},
+            "config": config_block(args, cfg, world),
+            "detail": {"iterations_timed": iters_dev, "iterations_per_s": iters_dev / (dev_ms * 1e-3),
+                       "samples_converged": n_ok, "us_per_iteration": dev_ms * 1e3 / max(1, iters_dev),
+                       "engine": "one process per GPU, one cooperative kernel launch per sample; all-gather / "
+                                 "reduce-scatter by peer stores from inside the kernel"},
             "clocks": clk,
             "e2e": {"value": K / (e2e_ms * 1e-3), "unit": "samples/s",
                     "h2d_bytes_per_step": 8 * (n_in + n_out), "d2h_bytes_per_step": C.sizeof(N.TrainResult),
@@ -345,24 +371,31 @@ def run_reference_child(args, cfg):
             return ok, max(wall, float(ms.value)), iters, text
 
         train_dir(os.path.join(tmp, "warm"))
+        # the reference arm must be the reference alone: none of this repository's native code
+        # may be mapped into the process that is being timed
+        mapped = sorted({l.split()[-1] for l in open("/proc/self/maps") if "hpnn_b200/lib" in l})
+        if mapped and not shim:
+            raise RuntimeError("reference arm has this repository's library mapped: %s" % mapped)
         clocks = ClockSampler(0)
         clocks.start()
         ok, ms, iters, text = train_dir(os.path.join(tmp, "timed"))
         clk = clocks.stop()
         K = args.steps
         out.update({
-            "metric": "train_nn samples/s (per-sample convergent %s training, fp64)" % train,
+            "metric": metric_name(cfg),
             "value": K / (ms * 1e-3), "unit": "samples/s", "n_gpus": n_gpus, "steps": K, "warmup": args.warmup,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp64",
-            "data": "synthetic (same files, seed and visiting order as the ours arm)",
-            "config": {"model": "%s %s" % (typ, "-".join(str(d) for d in [n_in, *hid, n_out])), "name": args.config,
-                       "baseline_config": desc, "global_batch": 1, "seq_len": None,
-                       "parallelism": ("hpnn-b200 through the libhpnn C API, row split over %d GPU(s), one process" % n_gpus) if shim else
+            "data": "synthetic (uniform [0,1) inputs, one-hot targets), random-init weights "
+                    "(glibc random(), seed %d)" % SEED,
+            "config": config_block(args, cfg, n_gpus),
+            "detail": {"iterations_timed": sum(iters), "iterations_per_s": sum(iters) / (ms * 1e-3),
+                       "samples_converged": len(re.findall(r"SUCCESS", text)),
+                       "us_per_iteration": ms * 1e3 / max(1, sum(iters)),
+                       "engine": ("hpnn-b200 through the libhpnn C API, row split over %d GPU(s), one process" % n_gpus) if shim else
                        "reference row split over %d GPU(s) x %d stream(s), one process" % (n_gpus, args.ref_streams),
                        "build": "hpnn_b200/lib/libhpnn.so (drop-in shim over the sm_100a engine)" if shim else
                        "unmodified sources, -D_OMP -D_CUDA -D_CUBLAS, nvcc sm_100 (baseline/build_ref.py)",
-                       "iterations_timed": sum(iters), "iterations_per_s": sum(iters) / (ms * 1e-3),
-                       "samples_converged": len(re.findall(r"SUCCESS", text))},
+                       "native_libraries_of_this_repo_mapped": mapped},
             "clocks": clk,
             "e2e": {"value": K / (ms * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": 8 * (n_in + n_out),
                     "d2h_bytes_per_step": 8 * n_out, "api": "nn_train_kernel(conf) (src/libhpnn.c:1149)"},
