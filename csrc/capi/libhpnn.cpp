@@ -8,7 +8,9 @@
 #include <string.h>
 #include <time.h>
 
+#include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "hpnn_core.h"
@@ -22,9 +24,13 @@ nn_runtime lib_runtime;  // one runtime per process, as in the reference (src/li
 
 namespace {
 
-// The object behind nn_def.kernel / kernel_ann*.  `pub` must stay the first member.
+// The object behind nn_def.kernel / kernel_ann*.  Kernels made by ann_generate / ann_load /
+// nn_load_conf hand out &own; a kernel_ann the CALLER allocated and passed to ann_kernel_allocate
+// (the reference's contract, include/libhpnn/ann.h:59, src/ann.c:113-202) is tracked by its address
+// and refreshed in place.  Nothing is ever read behind a kernel_ann* that is not in the registry.
 struct Shim {
-  kernel_ann pub;
+  kernel_ann own;
+  kernel_ann *pub = nullptr;  // &own, or the caller's struct
   hpnn_kernel *host = nullptr;
   hpnn_net *dev = nullptr;
   bool dev_newer = false;   // device weights are ahead of the host mirror
@@ -36,7 +42,24 @@ struct Shim {
   std::string name;
 };
 
-Shim *as_shim(kernel_ann *k) { return reinterpret_cast<Shim *>(k); }
+std::mutex g_reg_mu;
+std::unordered_map<const kernel_ann *, Shim *> g_registry;
+
+// the Shim behind a public kernel pointer, or nullptr for pointers this library does not know
+Shim *as_shim(const kernel_ann *k) {
+  if (!k) return nullptr;
+  std::lock_guard<std::mutex> g(g_reg_mu);
+  auto it = g_registry.find(k);
+  return it == g_registry.end() ? nullptr : it->second;
+}
+void register_shim(Shim *s) {
+  std::lock_guard<std::mutex> g(g_reg_mu);
+  g_registry[s->pub] = s;
+}
+void unregister_shim(Shim *s) {
+  std::lock_guard<std::mutex> g(g_reg_mu);
+  g_registry.erase(s->pub);
+}
 
 int g_gpu_cap = 0;          // nn_set_n_gpu: 0 = all
 bool g_cuda_ready = false;  // nn_init_CUDA succeeded
@@ -48,7 +71,7 @@ bool use_device() {
 void refresh_views(Shim *s) {
   hpnn_kernel *h = s->host;
   const int NL = hpnn_kernel_n_layers(h);
-  kernel_ann &k = s->pub;
+  kernel_ann &k = *s->pub;
   k.n_inputs = (UINT)hpnn_kernel_dim(h, 0);
   k.n_hiddens = (UINT)(NL - 1);
   k.n_outputs = (UINT)hpnn_kernel_dim(h, NL);
@@ -88,8 +111,10 @@ void refresh_views(Shim *s) {
 Shim *wrap(hpnn_kernel *h) {
   if (!h) return nullptr;
   Shim *s = new Shim();
-  memset(&s->pub, 0, sizeof(s->pub));
+  memset(&s->own, 0, sizeof(s->own));
+  s->pub = &s->own;
   s->host = h;
+  register_shim(s);
   refresh_views(s);
   const int NL = hpnn_kernel_n_layers(h);
   unsigned long cpu_bytes = 0;
@@ -156,6 +181,10 @@ void fill_opts(hpnn_train_opts *o, int type, int train, double alpha, double del
 // per-sample convergence loop + the reference's log line (src/ann.c:2322-2366)
 double train_sample(kernel_ann *kernel, int type, int train, DOUBLE *in, DOUBLE *out, DOUBLE alpha, DOUBLE delta) {
   Shim *s = as_shim(kernel);
+  if (!s || !s->host) {
+    NN_ERROR(stderr, "training step failed: not a kernel of this library\n");
+    return 0.;
+  }
   hpnn_train_result r;
   memset(&r, 0, sizeof(r));
   hpnn_train_opts o;
@@ -167,6 +196,7 @@ double train_sample(kernel_ann *kernel, int type, int train, DOUBLE *in, DOUBLE 
     s->dev_newer = true;
     memcpy(kernel->in, in, sizeof(double) * kernel->n_inputs);
   } else {
+    sync_to_host(s);  // the device may hold newer weights (CUDA switched off after device training)
     rc = hpnn_cpu_train_sample(s->host, &o, in, out, &r, nullptr);
     if (s->dev) s->dev_stale = true;
     refresh_views(s);
@@ -190,10 +220,14 @@ double train_sample(kernel_ann *kernel, int type, int train, DOUBLE *in, DOUBLE 
 
 void run_once(kernel_ann *kernel, int type) {
   Shim *s = as_shim(kernel);
+  if (!s || !s->host) return;
   hpnn_net *dev = device_for(s, type, s->dev_momentum);
   if (dev) {
+    // only the output vector comes back; the hidden layers' `vec` keep their previous contents
+    // on the device path (the reference's ann_kernel_run fills every vec, src/ann.c:892-1242)
     hpnn_net_run(dev, kernel->in, kernel->output.vec, 0);
   } else {
+    sync_to_host(s);
     hpnn_cpu_forward_inplace(s->host, type, 0);
   }
 }
@@ -202,6 +236,7 @@ double single_iteration(kernel_ann *kernel, int type, int train, const DOUBLE *t
   // the single-iteration entry points work on the host mirror (momentum must persist between
   // calls, which the per-sample device kernel deliberately does not do)
   Shim *s = as_shim(kernel);
+  if (!s || !s->host) return 0.;
   sync_to_host(s);
   hpnn_train_opts o;
   fill_opts(&o, type, train, alpha, -1., use_device());
@@ -499,8 +534,9 @@ void nn_dump_conf(nn_def *c, FILE *fp) {
   pc.tests = c->tests;
   std::vector<int> dims;
   if (c->kernel) {  // sizes are printed for generated kernels too (the reference prints 0, quirk 3)
-    hpnn_kernel *h = as_shim((kernel_ann *)c->kernel)->host;
-    for (int i = 0; i <= hpnn_kernel_n_layers(h); ++i) dims.push_back(hpnn_kernel_dim(h, i));
+    Shim *ks = as_shim((kernel_ann *)c->kernel);
+    hpnn_kernel *h = ks ? ks->host : nullptr;
+    for (int i = 0; h && i <= hpnn_kernel_n_layers(h); ++i) dims.push_back(hpnn_kernel_dim(h, i));
   }
   hpnn_conf_dump(&pc, (int)dims.size(), dims.empty() ? nullptr : dims.data(), fp);
 }
@@ -511,7 +547,10 @@ static bool ann_like(nn_def *c) { return c && (c->type == NN_TYPE_ANN || c->type
 void nn_free_kernel(nn_def *c) {
   if (!ann_like(c) || !c->kernel) return;
   ann_kernel_free((kernel_ann *)c->kernel);
-  delete as_shim((kernel_ann *)c->kernel);
+  if (Shim *ks = as_shim((kernel_ann *)c->kernel)) {  // still registered: a library-made kernel
+    unregister_shim(ks);
+    delete ks;
+  }
   c->kernel = NULL;
 }
 BOOL nn_generate_kernel(nn_def *c, ...) {
@@ -596,7 +635,7 @@ BOOL nn_train_kernel(nn_def *c) {
     FREE(in);
     FREE(out);
   }
-  sync_to_host(as_shim(k));
+  if (Shim *ks = as_shim(k)) sync_to_host(ks);
   if (host_momentum) ann_momentum_free(k);
   return TRUE;
 }
@@ -651,6 +690,10 @@ void nn_run_kernel(nn_def *c) {
   hpnn_shuffle_order(c->seed, (int)files.size(), order.data());
   const int type = c->type == NN_TYPE_SNN ? HPNN_TYPE_SNN : HPNN_TYPE_ANN;
   Shim *s = as_shim(k);
+  if (!s || !s->host) {
+    NN_ERROR(stderr, "nn_run_kernel: the configuration's kernel was not created by this library\n");
+    return;
+  }
   // Fast path (same verdicts, far fewer host round trips): parse every file in parallel, push the
   // whole directory through the batched FP64 forward.  HPNN_RUN_BATCH=0 restores one launch per file.
   const char *rb = getenv("HPNN_RUN_BATCH");
@@ -703,31 +746,45 @@ void nn_run_kernel(nn_def *c) {
 }
 
 /* ============================ model layer: ann.h ========================== */
+// Releases the storage behind a kernel.  A kernel of ann_generate / ann_load stays registered
+// (its struct is zeroed, nn_free_kernel deletes the object); a caller-owned struct that went
+// through ann_kernel_allocate is forgotten altogether, the struct itself remains the caller's.
 BOOL ann_kernel_free(kernel_ann *kernel) {
-  if (!kernel) return FALSE;
   Shim *s = as_shim(kernel);
+  if (!s) return FALSE;  // not ours (or already released): nothing behind it may be touched
   drop_device(s);
   if (s->host) hpnn_kernel_destroy(s->host);
   s->host = nullptr;
-  memset(&s->pub, 0, sizeof(s->pub));
+  memset(s->pub, 0, sizeof(*s->pub));
+  if (s->pub != &s->own) {
+    unregister_shim(s);
+    delete s;
+  }
   return TRUE;
 }
 
-// The reference fills a caller-provided struct; here the storage behind a kernel is managed
-// by the library, so this entry point only works on kernels that came from ann_generate /
-// ann_load (it re-shapes them).  Stand-alone use: call ann_generate instead.
+// Reference contract (src/ann.c:113-202): the caller ALLOCs a kernel_ann and this call fills
+// it.  The weights and work vectors it points to afterwards are owned by the library and live
+// until ann_kernel_free(kernel).  Called on a kernel of ann_generate / ann_load it re-shapes that
+// kernel (weights zeroed).
 BOOL ann_kernel_allocate(kernel_ann *kernel, UINT n_inputs, UINT n_hiddens, UINT *h_neurons, UINT n_outputs) {
   if (!kernel || !h_neurons || n_hiddens < 1) return FALSE;
-  Shim *s = as_shim(kernel);
-  if (!s->host) return FALSE;
   std::vector<int> dims;
   dims.push_back((int)n_inputs);
   for (UINT i = 0; i < n_hiddens; ++i) dims.push_back((int)h_neurons[i]);
   dims.push_back((int)n_outputs);
   hpnn_kernel *h = hpnn_kernel_create((int)dims.size(), dims.data());
   if (!h) return FALSE;
-  drop_device(s);
-  hpnn_kernel_destroy(s->host);
+  Shim *s = as_shim(kernel);
+  if (!s) {  // a struct of the caller's: track it by address, never read behind it
+    s = new Shim();
+    memset(&s->own, 0, sizeof(s->own));
+    s->pub = kernel;
+    register_shim(s);
+  } else {
+    drop_device(s);
+    if (s->host) hpnn_kernel_destroy(s->host);
+  }
   s->host = h;
   refresh_views(s);
   return TRUE;
@@ -735,7 +792,7 @@ BOOL ann_kernel_allocate(kernel_ann *kernel, UINT n_inputs, UINT n_hiddens, UINT
 
 kernel_ann *ann_load(CHAR *f_kernel) {
   Shim *s = wrap(hpnn_kernel_load(f_kernel));
-  return s ? &s->pub : NULL;
+  return s ? s->pub : NULL;
 }
 
 kernel_ann *ann_generate(UINT *seed, UINT n_inputs, UINT n_hiddens, UINT n_outputs, UINT *hiddens) {
@@ -747,7 +804,7 @@ kernel_ann *ann_generate(UINT *seed, UINT n_inputs, UINT n_hiddens, UINT n_outpu
   unsigned s0 = seed ? *seed : 0;
   Shim *s = wrap(hpnn_kernel_generate(&s0, (int)dims.size(), dims.data()));
   if (seed) *seed = s0;
-  return s ? &s->pub : NULL;
+  return s ? s->pub : NULL;
 }
 
 void ann_dump(kernel_ann *kernel, FILE *out) {
@@ -756,6 +813,10 @@ void ann_dump(kernel_ann *kernel, FILE *out) {
     return;
   }
   Shim *s = as_shim(kernel);
+  if (!s || !s->host) {
+    NN_ERROR(stderr, "CAN'T SAVE KERNEL! not a kernel of this library\n");
+    return;
+  }
   sync_to_host(s);
   if (hpnn_compat_is_root()) hpnn_kernel_dump(s->host, out);
 }
@@ -778,8 +839,8 @@ DOUBLE ann_kernel_train(kernel_ann *kernel, const DOUBLE *train) {
   return kernel ? single_iteration(kernel, HPNN_TYPE_ANN, HPNN_TRAIN_BP, train, 0.) : 0.;
 }
 void ann_momentum_init(kernel_ann *kernel) {
-  if (!kernel) return;
   Shim *s = as_shim(kernel);
+  if (!s || !s->host) return;
   hpnn_cpu_momentum_init(s->host);
   refresh_views(s);
   unsigned long bytes = 0;
@@ -788,11 +849,12 @@ void ann_momentum_init(kernel_ann *kernel) {
   NN_OUT(stdout, "[CPU] MOMENTUM ALLOC: %lu (bytes)\n", bytes);  // src/ann.c:1904-1907
 }
 void ann_raz_momentum(kernel_ann *kernel) {
-  if (kernel) hpnn_cpu_momentum_zero(as_shim(kernel)->host);
+  Shim *s = as_shim(kernel);
+  if (s && s->host) hpnn_cpu_momentum_zero(s->host);
 }
 void ann_momentum_free(kernel_ann *kernel) {
-  if (!kernel) return;
   Shim *s = as_shim(kernel);
+  if (!s || !s->host) return;
   hpnn_cpu_momentum_free(s->host);
   refresh_views(s);
 }

@@ -115,6 +115,12 @@ hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gp
     hpnn::set_error_msg("hpnn_net_create: no CUDA device");
     return nullptr;
   }
+  if ((int)k->dims.size() - 1 > HPNN_MAX_LAYERS) {
+    // the host kernel, the file formats and the CPU engine take any depth (like the reference);
+    // only the fixed-size device descriptor is capped, and callers fall back to the CPU engine
+    hpnn::set_error_msg("hpnn_net_create: more than HPNN_MAX_LAYERS weight layers (CPU engine only)");
+    return nullptr;
+  }
   if (n_gpus <= 0 || n_gpus > avail) n_gpus = avail;
   if (n_gpus > HPNN_MAX_WORLD) n_gpus = HPNN_MAX_WORLD;
   hpnn_net *n = new hpnn_net();

@@ -101,7 +101,7 @@ void hpnn_free(void *p) { free(p); }
 
 /* ------------------------------ kernel object ---------------------------- */
 hpnn_kernel *hpnn_kernel_create(int n_dims, const int *dims) {
-  if (n_dims < 3 || n_dims > HPNN_MAX_LAYERS + 1 || !dims) return nullptr;
+  if (n_dims < 3 || n_dims > (1 << 16) || !dims) return nullptr;  // any depth: only device nets are capped
   for (int i = 0; i < n_dims; ++i)
     if (dims[i] < 1) return nullptr;
   hpnn_kernel *k = new hpnn_kernel();
@@ -177,7 +177,6 @@ hpnn_kernel *hpnn_kernel_load(const char *path) {
   if (dims.size() < 3) return fail("parameter line has too few parameters!");
   for (int d : dims)
     if (d < 1) return fail("zero in parameter line!");
-  if ((int)dims.size() > HPNN_MAX_LAYERS + 1) return fail("too many layers for this build");
   k = hpnn_kernel_create((int)dims.size(), dims.data());
   if (!k) return fail("allocation failed");
   hpnn_kernel_set_name(k, name.c_str());
@@ -304,7 +303,7 @@ hpnn_kernel *hpnn_kernel_load_binary(const char *path) {
   hpnn_kernel *k = nullptr;
   std::vector<int> dims;
   bool ok = fread(magic, 1, 8, fp) == 8 && !memcmp(magic, BIN_MAGIC, 8) && fread(&nd, 4, 1, fp) == 1 &&
-            nd >= 3 && nd <= HPNN_MAX_LAYERS + 1;
+            nd >= 3 && nd <= (1 << 16);
   if (ok) {
     dims.resize(nd);
     ok = fread(dims.data(), 4, nd, fp) == (size_t)nd && fread(&nl, 4, 1, fp) == 1 && nl < (1 << 20);

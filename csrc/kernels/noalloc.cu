@@ -15,17 +15,28 @@
 //
 // Cost and limits, stated plainly:
 //   * the array is HPNN_NOALLOC_SCRATCH_BYTES (1 MiB + 1 KiB) of global memory on EVERY GPU
-//     that loads this library, from load until the process exits, used or not;
-//   * a network fits if its arena layout (hpnn_dev_arena_layout) needs no more than
-//     HPNN_NOALLOC_MAX_DOUBLES doubles -- roughly: three times the sum of the layer widths
-//     below ~40 000.  Larger networks are refused with an error, nothing is launched;
+//     on which this entry point has been called, until the process exits.  CUDA loads modules
+//     lazily by default, so the driver reserves the array (and the kernel image) during the
+//     FIRST call on a device, not when the library is mapped: that first call does allocate
+//     inside the driver.  A host that is about to hand the rest of the GPU to its own pool
+//     makes one call per device before doing so (or sets CUDA_MODULE_LOADING=EAGER);
+//   * a network fits if its arena layout (hpnn_dev_arena_layout, forward-pass regions only)
+//     needs no more than HPNN_NOALLOC_MAX_DOUBLES doubles.  The layout reserves, per layer
+//     output of width d, two double buffers of {value, tag} pairs (4 pad8(d)) and the partial-sum
+//     slots of the trainers (8 pad8(d)):
+//         need = pad8(n_in) + 12 * sum of pad8(d) over hidden and output widths
+//                + 2 * pad8(n_out) + 16,
+//     so the hidden and output widths may add up to about 10 900 (784-5000-5000-10 fits,
+//     784-20000-10 does not).  Larger networks are refused with an error, nothing is launched;
 //   * there is one array per GPU and every call uses it.  It still holds whatever the last
 //     call left there, so the part this call will use is cleared first (the kernel relies on
 //     zero padding behind every vector and on barrier words that start from a known state).
 //     Two calls whose GPU work overlaps -- different streams, or different host threads on
 //     the same device -- race on it; serialise them on one stream.
 //   * the first call on each device looks up the array's device address (see below).  That
-//     first call should be made during start-up, before any stream capture is begun.
+//     first call should be made during start-up, before any stream capture is begun.  The
+//     address is cached per device for the life of the process; it does not survive a
+//     cudaDeviceReset by the host.
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>

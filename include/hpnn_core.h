@@ -298,18 +298,23 @@ int hpnn_net_forward_batch(hpnn_net *n, const double *X, int batch, double *Y, i
  * Hosts that gave the whole GPU to their own pool, or that cannot afford the device-wide
  * synchronisation cudaMalloc/cudaFree imply, pass the padded weight matrices, the input and
  * the output buffer (all device memory they already own); the persistent kernel's work space
- * is a fixed array inside the library instead: HPNN_NOALLOC_SCRATCH_BYTES on every GPU that
- * loads the library, held until the process exits.
+ * is a fixed array inside the library instead: HPNN_NOALLOC_SCRATCH_BYTES on every GPU the
+ * entry point has been called on, held until the process exits.
  *   type / stable_softmax  as in hpnn_train_opts
  *   dims[0..n_layers]      layer widths; W[l] is [dims[l+1] x pad8(dims[l])], pad columns zero
  *   x (dims[0] doubles)    input;  out (dims[n_layers] doubles) receives the activated /
  *                          soft-maxed output; the call is asynchronous on `stream`
  * Returns 0, -1 on bad arguments or a CUDA error, -2 when the network's arena layout needs
- * more than HPNN_NOALLOC_MAX_DOUBLES doubles (nothing is launched; see hpnn_last_error()).
+ * more than HPNN_NOALLOC_MAX_DOUBLES doubles (nothing is launched; see hpnn_last_error()):
+ *   need = pad8(dims[0]) + 12 * sum_{i>=1} pad8(dims[i]) + 2 * pad8(dims[n_layers]) + 16,
+ * i.e. the hidden and output widths may add up to about 10 900.
  * It calls no cudaMalloc/cudaFree.  All calls on a device share the one array: calls whose
  * GPU work overlaps race, so keep them on one stream.  The first call on each device resolves
- * the array's address (cudaGetSymbolAddress); make that call at start-up, before any stream
- * capture begins. */
+ * the array's address (cudaGetSymbolAddress) and, because CUDA loads modules lazily, is also
+ * the moment the driver reserves the array and the kernel image: make that call at start-up,
+ * before any stream capture begins and before the host hands the rest of the GPU to its own
+ * pool (or run with CUDA_MODULE_LOADING=EAGER).  The cached address does not survive a
+ * cudaDeviceReset by the host. */
 #define HPNN_NOALLOC_MAX_DOUBLES (128 * 1024)
 #define HPNN_NOALLOC_SCRATCH_BYTES (HPNN_NOALLOC_MAX_DOUBLES * 8 + 1024)
 int hpnn_dev_forward_noalloc(int type, int stable_softmax, int n_layers, const int *dims,

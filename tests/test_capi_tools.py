@@ -265,3 +265,61 @@ def test_checkpoint_and_metrics(tmp_path):
     assert k_txt.dims == k_bin.dims == [8, 5, 4, 3]
     for a, b in zip(k_bin.weights, conf.kernel.weights):  # last checkpoint == end of pass (6 % 2 == 0)
         assert (a == b).all()
+
+
+MODEL_LAYER_C = r"""
+#include <stdio.h>
+#include <string.h>
+#include <libhpnn.h>
+#include <libhpnn/ann.h>
+#include <libhpnn/snn.h>
+/* the reference's contract for ann_kernel_allocate: the CALLER owns the struct (include/libhpnn/ann.h:59,
+ * src/ann.c:113-202); and no entry point may read behind a kernel_ann it has never seen */
+int main(void){
+    kernel_ann mine, stranger;
+    UINT hid[2]={5,4};
+    DOUBLE in[8]={.1,.2,.3,.4,.5,.6,.7,.8}, out[3]={1.,-1.,-1.};
+    memset(&mine,0,sizeof(mine)); memset(&stranger,0,sizeof(stranger));
+    nn_init_all(0);
+    /* unknown pointers: every call must refuse or do nothing */
+    if(ann_kernel_free(&stranger)!=FALSE) return 1;
+    ann_kernel_run(&stranger); ann_raz_momentum(&stranger); ann_momentum_init(&stranger); ann_momentum_free(&stranger);
+    if(ann_kernel_train(&stranger,out)!=0.) return 2;
+    if(ann_train_BP(&stranger,in,out,-1.)!=0.) return 3;
+    ann_dump(&stranger,stdout);
+    /* caller-owned struct */
+    if(ann_kernel_allocate(&mine,8,2,hid,3)!=TRUE) return 4;
+    if(mine.n_inputs!=8||mine.n_hiddens!=2||mine.n_outputs!=3||!mine.in||!mine.output.weights) return 5;
+    if(mine.hiddens[0].n_neurons!=5||mine.hiddens[1].n_inputs!=5||mine.output.n_inputs!=4) return 6;
+    if(ann_validate_kernel(&mine)!=TRUE) return 7;
+    for(UINT i=0;i<5*8;i++) mine.hiddens[0].weights[i]=0.01*(double)(i%7)-0.02;
+    for(UINT i=0;i<4*5;i++) mine.hiddens[1].weights[i]=0.02*(double)(i%5)-0.03;
+    for(UINT i=0;i<3*4;i++) mine.output.weights[i]=0.03*(double)(i%3)-0.02;
+    memcpy(mine.in,in,sizeof(in));
+    ann_kernel_run(&mine);
+    printf("o0=%.12f\n",mine.output.vec[0]);
+    DOUBLE d=ann_kernel_train(&mine,out);
+    printf("dE=%.6e\n",d);
+    if(!(d>0.)) return 8;
+    if(ann_kernel_free(&mine)!=TRUE) return 9;
+    if(mine.in!=NULL||mine.n_inputs!=0) return 10;
+    if(ann_kernel_free(&mine)!=FALSE) return 11; /* second free: unknown again */
+    nn_deinit_all();
+    printf("MODEL_LAYER_OK\n");
+    return 0;
+}
+"""
+
+
+def test_model_layer_caller_allocated_kernel(artefacts, tmp_path):
+    """ann_kernel_allocate fills a struct the caller allocated, and pointers the library
+    has never seen are refused instead of being reinterpreted."""
+    src = tmp_path / "model_layer.c"
+    src.write_text(MODEL_LAYER_C)
+    exe = tmp_path / "model_layer"
+    r = subprocess.run(["gcc", "-O1", "-g", f"-I{ROOT}/include", str(src), "-o", str(exe), f"-L{LIBDIR}", "-lhpnn",
+                        f"-Wl,-rpath,{LIBDIR}", "-lm"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = _run([str(exe)], tmp_path)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "MODEL_LAYER_OK" in r.stdout

@@ -127,3 +127,24 @@ def test_packed_sample_loop_equals_single_step_path_bitwise(nn_type, train, thre
             b.close()
     finally:
         lib.hpnn_set_omp_threads(0)
+
+
+def test_deep_network_beyond_the_device_cap(tmp_path):
+    """The reference accepts any number of hidden layers (src/ann.c:206-766); only the device
+    descriptor is capped at HPNN_MAX_LAYERS, so host kernels, kernel files and the CPU engine
+    must take a deeper net."""
+    import hpnn_b200 as hp
+    from hpnn_b200 import _native as N
+    from hpnn_b200.trainer import CpuEngine
+
+    hid = [6] * 20  # 21 weight layers > HPNN_MAX_LAYERS
+    k, _ = hp.generate_kernel(5, 7, hid, 3)
+    path = tmp_path / "deep.kernel"
+    hp.dump_kernel(k, str(path))
+    k2 = hp.load_kernel(str(path))
+    assert list(k2.dims) == [7] + hid + [3]
+    cpu = CpuEngine(k2, N.TYPE_ANN, N.TRAIN_BP, max_iter=40)
+    r = cpu.train(np.linspace(0.1, 0.9, 7), np.array([1.0, -1.0, -1.0]))
+    assert r.n_iter >= 1 and np.isfinite(r.last_err)
+    assert cpu.run(np.linspace(0.1, 0.9, 7)).shape == (3,)
+    cpu.close()

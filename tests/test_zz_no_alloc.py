@@ -72,3 +72,54 @@ def test_networks_beyond_the_built_in_scratch_are_refused():
     msg = lib.hpnn_last_error().decode()
     assert "HPNN_NOALLOC_MAX_DOUBLES" in msg and "doubles" in msg
     assert fn(hp.TYPE_ANN, 0, 1, dims, ws, dummy.data_ptr(), dummy.data_ptr(), None) == -1  # no hidden layer
+
+
+def _need(dims):
+    """Work-space doubles of a forward pass (the formula documented in include/hpnn_core.h)."""
+    pad8 = lambda v: (v + 7) & ~7
+    return pad8(dims[0]) + 12 * sum(pad8(d) for d in dims[1:]) + 2 * pad8(dims[-1]) + 16
+
+
+def test_documented_limit_is_the_real_one():
+    """Largest accepted and smallest refused hidden width for an 8-h-8 network, straight from the
+    documented formula; the accepted one must also compute the right answer."""
+    lib, fn = _bind()
+    limit = 128 * 1024
+    h_ok = max(h for h in range(10000, 11000, 8) if _need([8, h, 8]) <= limit)
+    h_bad = h_ok + 8
+    assert _need([8, h_ok, 8]) <= limit < _need([8, h_bad, 8])
+    k, _ = hp.generate_kernel(3, 8, [h_ok], 8)
+    net = HpnnNet(k, hp.TYPE_ANN, momentum=False)
+    x = torch.linspace(0.05, 0.95, 8, dtype=torch.float64, device="cuda")
+    want = net.run(x).clone()
+    torch.testing.assert_close(_call(fn, hp.TYPE_ANN, net, x), want, atol=1e-13, rtol=0)
+    net.close()
+    dims = (C.c_int * 3)(8, h_bad - 7, 8)  # pads up to h_bad
+    dummy = torch.zeros(8, dtype=torch.float64, device="cuda")
+    ws = (C.c_void_p * 2)(dummy.data_ptr(), dummy.data_ptr())
+    assert fn(hp.TYPE_ANN, 0, 2, dims, ws, dummy.data_ptr(), dummy.data_ptr(), None) == -2
+    # the examples quoted in the documentation
+    assert _need([784, 5000, 5000, 10]) <= limit < _need([784, 20000, 10])
+
+
+def test_repeated_calls_leave_device_memory_untouched():
+    """The point of the entry point: once the first call on a device is behind us (module load,
+    address look-up), further calls must not change the amount of free device memory."""
+    lib, fn = _bind()
+    k, _ = hp.generate_kernel(5, 64, [48, 40], 10)
+    net = HpnnNet(k, hp.TYPE_SNN, momentum=False)
+    x = torch.rand(64, dtype=torch.float64, device="cuda")
+    dims = (C.c_int * len(net.dims))(*net.dims)
+    ws = (C.c_void_p * net.n_layers)(*[w.data_ptr() for w in net.W_full])
+    out = torch.empty(10, dtype=torch.float64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    assert fn(hp.TYPE_SNN, 0, net.n_layers, dims, ws, x.data_ptr(), out.data_ptr(), stream) == 0  # first call
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(20):
+        assert fn(hp.TYPE_SNN, 0, net.n_layers, dims, ws, x.data_ptr(), out.data_ptr(), stream) == 0
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0
+    assert abs(float(out.sum()) - 1.0) < 1e-12  # a soft-max came out
+    net.close()
