@@ -262,9 +262,8 @@ __host__ __device__ inline int row_part_doubles(int rows, int grid) { return ((r
 template <int UPD>
 __device__ __forceinline__ void phase_rows(double *W, double *dW, int ld, int rows, const double *xs,
                                            const double *ds, double lr, double alpha, int act_kind,
-                                           const Dst &dst, int segs, double *rowpart) {
+                                           const Dst &dst, int segs, double *rowpart, int grid, int b) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int grid = gridDim.x, b = blockIdx.x;
   const int mine = b < rows ? (rows - b + grid - 1) / grid : 0;  // rows b, b+grid, ...
   const int n2 = ld >> 1;
   const int seg2 = (n2 + segs - 1) / segs;  // double2 per segment
@@ -384,11 +383,11 @@ __device__ __forceinline__ void col_task(double *W, double *dW, int ld, int row_
 template <int UPD, typename SinkFactory>
 __device__ __forceinline__ void phase_cols(double *W, double *dW, int ld, int rows, int cb, int rsplit, const double *ds,
                                            const double *h, bool h_shared, double lr, double alpha, double *red,
-                                           SinkFactory make_sink) {
+                                           SinkFactory make_sink, int grid, int b) {
   const int ncb = ld / cb;
   const int ntasks = ncb * rsplit;
   const int part_rows = (rows + rsplit - 1) / rsplit;
-  for (int t = blockIdx.x; t < ntasks; t += gridDim.x) {
+  for (int t = b; t < ntasks; t += grid) {
     const int c0 = (t % ncb) * cb, rp = t / ncb;
     const int rb = rp * part_rows, re = min(rows, rb + part_rows);
     auto sink = make_sink(c0, rp);

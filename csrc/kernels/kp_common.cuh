@@ -29,7 +29,7 @@ struct KP {
 //
 // Arrival is a fire-and-forget `red.release.gpu` on one of three rotating counters (no
 // round trip for a return value); everybody polls that counter with relaxed loads until it
-// reads gridDim.x and then issues one acquire fence.  CTA 0 zeroes the counter used by the
+// reads the number of CTAs of the rank and then issues one acquire fence.  CTA 0 zeroes the counter used by the
 // PREVIOUS barrier once it has passed the current one: all CTAs have left it by then, and it
 // is not needed again before barrier k+2, which cannot complete without CTA 0's own arrival
 // at k+1 (ordered after the reset).  The barrier index survives kernel launches in
@@ -41,9 +41,13 @@ struct KP {
 // local_sync words: [0],[32],[64] counters (own 128 B lines), [96] go, [128] saved index.
 struct Barrier {
   unsigned *sync;
-  unsigned k;  // barrier index, meaningful in thread 0
-  __device__ __forceinline__ void init(const hpnn_dev_net &n) {
+  unsigned k;     // barrier index, meaningful in thread 0
+  unsigned grid;  // CTAs of THIS rank (the whole grid, or the rank's share of a virtual-rank launch)
+  int bid;        // index of this CTA within the rank
+  __device__ __forceinline__ void init(const hpnn_dev_net &n, int grid_, int bid_) {
     sync = n.local_sync;
+    grid = (unsigned)grid_;
+    bid = bid_;
     k = (threadIdx.x == 0) ? ld_relaxed_gpu(sync + 128) : 0u;
   }
   // grid barrier of this GPU only (no cross-rank part, no system-scope fences)
@@ -54,15 +58,15 @@ struct Barrier {
       unsigned *prev = sync + 32 * ((k + 2u) % 3u);
       ++k;
       red_add_release_gpu(c, 1u);
-      while (ld_relaxed_gpu(c) != gridDim.x) {
+      while (ld_relaxed_gpu(c) != grid) {
       }
-      if (blockIdx.x == 0) *prev = 0;
+      if (bid == 0) *prev = 0;
       fence_gpu();
     }
     __syncthreads();
   }
   __device__ __forceinline__ void finish() {  // call once, after the last barrier
-    if (blockIdx.x == 0 && threadIdx.x == 0) sync[128] = k;
+    if (bid == 0 && threadIdx.x == 0) sync[128] = k;
   }
   // `remote`: this CTA stored into a peer's arena since the last barrier (only then does
   // it pay for a system-scope fence before arriving).
@@ -75,12 +79,12 @@ struct Barrier {
       if (n.world > 1 && remote) fence_sys();  // peer stores performed before the arrive
       red_add_release_gpu(c, 1u);
       if (n.world == 1) {
-        while (ld_relaxed_gpu(c) != gridDim.x) {
+        while (ld_relaxed_gpu(c) != grid) {
         }
-        if (blockIdx.x == 0) *prev = 0;
+        if (bid == 0) *prev = 0;
         fence_gpu();
-      } else if (blockIdx.x == 0) {
-        while (ld_relaxed_gpu(c) != gridDim.x) {
+      } else if (bid == 0) {
+        while (ld_relaxed_gpu(c) != grid) {
         }
         *prev = 0;
         const unsigned long long we = (unsigned long long)k;

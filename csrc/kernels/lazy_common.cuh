@@ -79,7 +79,7 @@ struct DotOut {
 
 // coef[j] = sum over the producers' chunks (rank-major, CTA order): v_j . x for the layer whose
 // input x was produced by the previous row phase.  rows_prev(q) = rows of that phase on rank q.
-__device__ __forceinline__ void gather_dots(const hpnn_dev_net &n, int l, int m, double *coef, double *red) {
+__device__ __forceinline__ void gather_dots(const hpnn_dev_net &n, int l, int m, double *coef, double *red, int grid) {
   const double *slots = n.arena[n.rank] + n.off_hist_dot[l];
   const int N = n.dims[l];  // rows of layer l-1, split over the ranks
   double acc[kLazyChunk];
@@ -88,7 +88,7 @@ __device__ __forceinline__ void gather_dots(const hpnn_dev_net &n, int l, int m,
   for (int idx = threadIdx.x; idx < n.world * kLazyDotSlots; idx += kThreads) {
     const int q = idx / kLazyDotSlots, b = idx % kLazyDotSlots;
     const int rows_q = row0_of(q + 1, N, n.world) - row0_of(q, N, n.world);
-    if (b < (int)gridDim.x && b < rows_q) chunk_fma(slots + (size_t)idx * kLazyChunk, 1.0, m, acc);
+    if (b < grid && b < rows_q) chunk_fma(slots + (size_t)idx * kLazyChunk, 1.0, m, acc);
   }
   chunk_block_sum(acc, m, coef, red);
 }

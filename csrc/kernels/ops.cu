@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   dst.n = 1;
   dst.tag = 0;
   dst.p[0] = y;
-  phase_rows<UPD>(W, dW, ld, rows, xs, ds, lr, alpha, act_kind, dst, pick_row_segments(rows, ld, gridDim.x), rowpart);
+  phase_rows<UPD>(W, dW, ld, rows, xs, ds, lr, alpha, act_kind, dst, pick_row_segments(rows, ld, gridDim.x), rowpart, gridDim.x, blockIdx.x);
 }
 
 // ------------------------------- K-B ---------------------------------------
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       if (c0 + i < cols) part[c0 + i] = v;
     };
   };
-  phase_cols<UPD>(W, dW, ld, rows, cb, 1, ds, h, false, lr, alpha, red, make_sink);
+  phase_cols<UPD>(W, dW, ld, rows, cb, 1, ds, h, false, lr, alpha, red, make_sink, gridDim.x, blockIdx.x);
 }
 
 __global__ void k_delta_finalize(const double *part, int n_parts, int stride, const double *h, int n,

@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_
   const int depth = p.lazy_depth;
 
   Barrier bar;
-  bar.init(n);
+  bar.init(n, gridDim.x, blockIdx.x);
   int trace_n = 0;
   auto trace = [&](int tag) {
     if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_
   auto forward = [&](int l, int src_buf, int dst_buf, int u, int m) {
     stage_vec(xs, act_of(n.rank, l, src_buf), pad8(n.dims[l]));
     __syncthreads();
-    if (l >= 1 && m > 0) gather_dots(n, l, m, coef, red);  // coef[j] = v_j . x
+    if (l >= 1 && m > 0) gather_dots(n, l, m, coef, red, gridDim.x);  // coef[j] = v_j . x
     Dst dst;
     dst.n = n.world;
     dst.tag = 0ull;

@@ -354,7 +354,7 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
 // tagged variant of gather_dots: every producer chunk is 8 {value, tag} pairs in this rank's arena,
 // polled until the tag of the running iteration shows up (no barrier, no fence)
 __device__ __forceinline__ void gather_dots_tagged(const hpnn_dev_net &n, int l, int m, unsigned long long tag,
-                                                   double *coef, double *red) {
+                                                   double *coef, double *red, int grid) {
   const double *slots = n.arena[n.rank] + n.off_hist_dot[l];
   const int N = n.dims[l];  // rows of layer l-1, split over the ranks
   double acc[kLazyChunk];
@@ -363,7 +363,7 @@ __device__ __forceinline__ void gather_dots_tagged(const hpnn_dev_net &n, int l,
   for (int idx = threadIdx.x; idx < n.world * kLazyDotSlots; idx += kThreads) {
     const int q = idx / kLazyDotSlots, b = idx % kLazyDotSlots;
     const int rows_q = row0_of(q + 1, N, n.world) - row0_of(q, N, n.world);
-    if (b < (int)gridDim.x && b < rows_q) {
+    if (b < grid && b < rows_q) {
       const double *addr[kLazyChunk];
       bool want[kLazyChunk];
       double v[kLazyChunk];
@@ -385,11 +385,10 @@ __device__ __forceinline__ void gather_dots_tagged(const hpnn_dev_net &n, int l,
 // grid barriers stay local to the GPU and there is no system-scope fence.  TG == false: plain
 // buffers + fence / flag barriers (also the single-rank case).
 template <bool TG>
-__global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid_constant__ KP p) {
+__device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int grid, const int b) {
   extern __shared__ double smem[];
   const hpnn_dev_net &n = p.net;
   const int NL = n.n_layers;
-  const int grid = gridDim.x, b = blockIdx.x;
   const int pmax = p.max_rows;  // here: widest panel, padded to 8 (see the launcher)
   double *xs = smem;                 // input vector of the running forward phase
   double *dsl = xs + p.max_ld;       // deltas of the own panel of the layer being processed
@@ -408,7 +407,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   auto tag_of = [&](int iteration) { return (launch << 32) | (unsigned long long)(unsigned)iteration; };
 
   Barrier bar;
-  bar.init(n);
+  bar.init(n, grid, b);
   int trace_n = 0;
   auto trace = [&](int tag) {
     if (p.trace && b == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
@@ -465,8 +464,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
     stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
     __syncthreads();
     if (l >= 1 && m > 0) {  // coef[j] = v_j . x
-      if (tg) gather_dots_tagged(n, l, m, tag, coef, red);
-      else gather_dots(n, l, m, coef, red);
+      if (tg) gather_dots_tagged(n, l, m, tag, coef, red, grid);
+      else gather_dots(n, l, m, coef, red, grid);
     }
     Dst dst;  // all-gather by peer stores
     dst.n = n.world;
@@ -708,10 +707,29 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid
   }
 }
 
-// 0 = launched, < 0 = error, 1 = not eligible.  HPNN_LAZY_PANEL=0 falls back to the column-task
-// variant of train_lazy.cu (which also serves every multi-rank job).
+template <bool TG>
+__global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1(const __grid_constant__ KP p) {
+  train_sample_lazy1_body<TG>(p, (int)gridDim.x, (int)blockIdx.x);
+}
+
+// several ranks of a row-split job inside ONE cooperative launch (see k_train_sample_vranks)
+template <bool TG>
+__global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1_vranks(const KP *pv, int ctas_per_rank) {
+  __shared__ KP sp;
+  const int vr = (int)blockIdx.x / ctas_per_rank, bid = (int)blockIdx.x % ctas_per_rank;
+  {
+    const unsigned long long *src = reinterpret_cast<const unsigned long long *>(pv + vr);
+    unsigned long long *dst = reinterpret_cast<unsigned long long *>(&sp);
+    static_assert(sizeof(KP) % 8 == 0, "KP is copied in 8-byte words");
+    for (int i = threadIdx.x; i < (int)(sizeof(KP) / 8); i += kThreads) dst[i] = src[i];
+  }
+  __syncthreads();
+  train_sample_lazy1_body<TG>(sp, ctas_per_rank, bid);
+}
+
 int g_lazy_panel = -1;  // -1 = HPNN_LAZY_PANEL (default on), 0 = off, 1 = on
-int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
+// Eligibility + launch parameters of K-PL1 for one rank: 0 = p_out / smem_out filled, 1 = not eligible.
+int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
   static const int disabled_env = [] {
     const char *e = getenv("HPNN_LAZY_PANEL");
     return (e && !strcmp(e, "0")) ? 1 : 0;
@@ -742,6 +760,17 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
   p.max_rows = pmax;  // the kernel's carve-up uses the panel height, not the layer height
   const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart);
   if (smem > 227 * 1024) return 1;
+  p_out = p;
+  smem_out = smem;
+  return 0;
+}
+
+// 0 = launched, < 0 = error, 1 = not eligible.  HPNN_LAZY_PANEL=0 falls back to the column-task
+// variant of train_lazy.cu.
+int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
+  KP p;
+  size_t smem = 0;
+  if (prepare_lazy1(p_in, grid, p, smem) != 0) return 1;
   const void *kfn = p.tagged ? (const void *)k_train_sample_lazy1<true> : (const void *)k_train_sample_lazy1<false>;
   cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) {
@@ -753,6 +782,23 @@ int launch_lazy1_if_eligible(const KP &p_in, int grid, void *stream) {
                                   (cudaStream_t)stream);
   if (e != cudaSuccess) {
     set_error("cudaLaunchCooperativeKernel(k_train_sample_lazy1)", e);
+    return -1;
+  }
+  return 0;
+}
+
+// virtual-rank launch of K-PL1 (every rank's KP already prepared, same smem for all)
+int launch_lazy1_vranks(const KP *pv_dev, int world, int ctas_per_rank, bool tagged, size_t smem, void *stream) {
+  const void *kfn = tagged ? (const void *)k_train_sample_lazy1_vranks<true> : (const void *)k_train_sample_lazy1_vranks<false>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(k_train_sample_lazy1_vranks)", e);
+    return -1;
+  }
+  void *args[] = {(void *)&pv_dev, (void *)&ctas_per_rank};
+  e = cudaLaunchCooperativeKernel(kfn, dim3(world * ctas_per_rank), dim3(kThreads), args, smem, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("cudaLaunchCooperativeKernel(k_train_sample_lazy1_vranks)", e);
     return -1;
   }
   return 0;

@@ -23,9 +23,11 @@
 
 namespace hpnn {
 
-// TG: tagged-pair hand-over between ranks (world > 1); false = plain buffers + barriers
+// TG: tagged-pair hand-over between ranks (world > 1); false = plain buffers + barriers.
+// grid / bid: CTAs of this rank and this CTA's index among them (the whole launch, except in
+// the virtual-rank launch below where several ranks share one cooperative grid).
 template <bool TG>
-__global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_constant__ KP p) {
+__device__ __forceinline__ void train_sample_body(const KP &p, const int grid, const int bid) {
   extern __shared__ double smem[];
   double *xs = smem;
   double *ds = xs + p.max_ld;
@@ -38,10 +40,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   double *A = n.arena[n.rank];
   const bool snn = p.type == HPNN_TYPE_SNN;
   const int upd = (p.train == HPNN_TRAIN_BPM) ? 2 : 1;
-  const int grid = gridDim.x;
 
   Barrier bar;
-  bar.init(n);
+  bar.init(n, grid, bid);
   // Several ranks: every vector that crosses NVLink is handed over as tagged pairs (no fences,
   // no cross-rank barrier); grid barriers stay local to the GPU.  p.tagged == 0 keeps the
   // fence + flag-word barrier (one rank, or HPNN_TP_PROTOCOL=barrier).
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   };
   int trace_n = 0;
   auto trace = [&](int tag) {
-    if (p.trace && blockIdx.x == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
+    if (p.trace && bid == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
       p.trace[2 * trace_n] = tag;
       p.trace[2 * trace_n + 1] = clock64();
       ++trace_n;
@@ -80,10 +81,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     dst.tag = tg ? tag : 0ull;
     for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + (size_t)n.row0[l] * (tg ? 2 : 1);
     const int kind = (snn && l == NL - 1) ? 1 : 0;
-    const int segs = pick_row_segments(n.rows[l], n.ld[l], gridDim.x);
-    if (u == 0) phase_rows<0>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, 0.0, 0.0, kind, dst, segs, rowpart);
-    else if (u == 1) phase_rows<1>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst, segs, rowpart);
-    else phase_rows<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst, segs, rowpart);
+    const int segs = pick_row_segments(n.rows[l], n.ld[l], grid);
+    if (u == 0) phase_rows<0>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, 0.0, 0.0, kind, dst, segs, rowpart, grid, bid);
+    else if (u == 1) phase_rows<1>(n.W[l], nullptr, n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst, segs, rowpart, grid, bid);
+    else phase_rows<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], xs, ds, p.lr, p.alpha, kind, dst, segs, rowpart, grid, bid);
   };
 
   // ---- prologue: zero the momentum (per sample, src/ann.c:2386), first forward
@@ -91,13 +92,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     for (int l = 0; l < NL; ++l) {
       double2 *m2 = reinterpret_cast<double2 *>(n.dW[l]);
       const size_t tot = (size_t)n.rows[l] * n.ld[l] / 2;
-      for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (size_t)grid * blockDim.x)
+      for (size_t i = (size_t)bid * blockDim.x + threadIdx.x; i < tot; i += (size_t)grid * blockDim.x)
         stg_cg2(m2 + i, make_double2(0.0, 0.0));
     }
   }
   for (int l = 0; l < NL; ++l) {
     forward_layer(l, cur, cur, 0, tag_of(0));
-    sync_phase((int)blockIdx.x < n.rows[l]);
+    sync_phase(bid < n.rows[l]);
   }
   const double *target = A + n.off_target;
   const int last = NL - 1;
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
     return output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, row0, rows, dsp, o_out, red);
   };
   OutStats st = evaluate(tag_of(0), n.row0[last], n.rows[last], ds,
-                         (p.mode == 1 && blockIdx.x == 0) ? A + n.off_out : nullptr);
+                         (p.mode == 1 && bid == 0) ? A + n.off_out : nullptr);
   double E = st.err;
   const double init_err = E;
   int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
@@ -151,22 +152,22 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
           __syncthreads();
           h = xs;
         }
-        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, tg, p.lr, p.alpha, red, make_sink);
-        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, tg, p.lr, p.alpha, red, make_sink);
+        if (upd == 1) phase_cols<1>(n.W[l], nullptr, n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, tg, p.lr, p.alpha, red, make_sink, grid, bid);
+        else phase_cols<2>(n.W[l], n.dW[l], n.ld[l], n.rows[l], cb, plan.rsplit, ds, h, tg, p.lr, p.alpha, red, make_sink, grid, bid);
         trace(100 + l);
-        sync_phase((int)blockIdx.x < (n.ld[l] / cb) * plan.rsplit);
+        sync_phase(bid < (n.ld[l] / cb) * plan.rsplit);
         trace(200 + l);
       }
       // ---- bottom-up: layer 0 update fused with its forward, then the rest
       stage_delta(n, 0, layer_plan(n, 1, grid).rsplit, act_of(n.rank, 1, cur), ds, tg, tag);
       forward_layer(0, 0, cur ^ 1, upd, tag);
       trace(300);
-      sync_phase((int)blockIdx.x < n.rows[0]);
+      sync_phase(bid < n.rows[0]);
       trace(400);
       for (int l = 1; l < NL; ++l) {
         forward_layer(l, cur ^ 1, cur ^ 1, 0, tag);
         trace(300 + l);
-        sync_phase((int)blockIdx.x < n.rows[l]);
+        sync_phase(bid < n.rows[l]);
         trace(400 + l);
       }
       cur ^= 1;
@@ -182,11 +183,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
       if (!(dE > p.thr || !ok)) break;
     }
     // publish the final (normalised) output vector
-    if (blockIdx.x == 0) evaluate(tag_of(iter), 0, 0, nullptr, A + n.off_out);
+    if (bid == 0) evaluate(tag_of(iter), 0, 0, nullptr, A + n.off_out);
   }
   bar.finish();
-  if (blockIdx.x == 0 && threadIdx.x == 0) n.local_sync[160] = (unsigned)launch;
-  if (blockIdx.x == 0 && threadIdx.x == 0 && p.result) {
+  if (bid == 0 && threadIdx.x == 0) n.local_sync[160] = (unsigned)launch;
+  if (bid == 0 && threadIdx.x == 0 && p.result) {
     hpnn_train_result r;
     r.init_err = init_err;
     r.final_de = dE;
@@ -199,12 +200,40 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_const
   }
 }
 
+template <bool TG>
+__global__ void __launch_bounds__(kThreads, 1) k_train_sample(const __grid_constant__ KP p) {
+  train_sample_body<TG>(p, (int)gridDim.x, (int)blockIdx.x);
+}
+
+// Virtual ranks: ONE cooperative launch hosts `world` ranks of a row-split job on one GPU, each
+// with its own weights slice, arena and sync words and gridDim.x / world CTAs.  It exists so that
+// the multi-rank protocols (peer stores, cross-rank barrier, tagged hand-over) can be verified
+// where only one GPU is available -- the successor of the reference's DEBUG build that fakes three
+// GPUs with three contexts on device 0 (include/libhpnn/common.h:511-572).  Ranks that wait on each
+// other must be co-resident, which separate launches on one GPU do not guarantee; a single
+// cooperative grid does.
+template <bool TG>
+__global__ void __launch_bounds__(kThreads, 1) k_train_sample_vranks(const KP *pv, int ctas_per_rank) {
+  __shared__ KP sp;
+  const int vr = (int)blockIdx.x / ctas_per_rank, bid = (int)blockIdx.x % ctas_per_rank;
+  {
+    const unsigned long long *src = reinterpret_cast<const unsigned long long *>(pv + vr);
+    unsigned long long *dst = reinterpret_cast<unsigned long long *>(&sp);
+    static_assert(sizeof(KP) % 8 == 0, "KP is copied in 8-byte words");
+    for (int i = threadIdx.x; i < (int)(sizeof(KP) / 8); i += kThreads) dst[i] = src[i];
+  }
+  __syncthreads();
+  train_sample_body<TG>(sp, ctas_per_rank, bid);
+}
+
 // defined in train_resident.cu: 0 = launched, < 0 = error, 1 = not eligible (use the streaming kernel)
 int launch_resident_if_eligible(const KP &p, int grid, void *stream);
 // defined in train_lazy.cu, same convention
 int launch_lazy_if_eligible(const KP &p, int grid, size_t smem, void *stream);
 // defined in train_lazy1.cu (one GPU, row panels), same convention
 int launch_lazy1_if_eligible(const KP &p, int grid, void *stream);
+int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out);
+int launch_lazy1_vranks(const KP *pv_dev, int world, int ctas_per_rank, bool tagged, size_t smem, void *stream);
 extern long long g_lazy_min_bytes;
 
 // ------------------------------- host side ---------------------------------
@@ -333,10 +362,10 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
   return off;
 }
 
-int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
-                          hpnn_train_result *result_dev, void *stream) {
-  if (!net || !o) return -1;
-  KP p;
+// Kernel parameters of one rank for a launch with `grid` CTAs per rank; smem_plain is the dynamic
+// shared memory of the streaming kernel (k_train_sample).  0 = ok.
+static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode, hpnn_train_result *result_dev,
+                    int grid, KP &p, size_t &smem_plain) {
   p.net = *net;
   hpnn_train_opts d;
   hpnn_train_opts_default(&d, o->type, o->train, 1);
@@ -351,13 +380,16 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   p.max_iter = o->max_iter >= 0 ? o->max_iter : d.max_iter;
   p.result = result_dev;
   {
-    // tagged hand-over wins when the phases are short (latency bound: 2x on SNN 784-1000-1000-10
-    // at 4 GPUs); with long bandwidth-bound phases the fence + flag barrier is cheaper than
-    // polling every vector (measured -7% on 8192-wide layers), so pick by local weight volume
+    // The tagged hand-over costs one NVLink flight per phase; the fence + flag barrier costs a
+    // system-scope fence (a round trip while peer stores are in flight) plus the flag flight and
+    // a relay through CTA 0, ~10 us on 8 GPUs.  Tagged therefore wins whenever a phase is short:
+    // always for nets that stream < 48 MB per rank, and for ANY net from 4 ranks on (a rank's
+    // share of an 8192 x 8192 layer streams in ~10 us at 8 ranks).  Polling every vector costs
+    // ~2% when the phases are long (2 ranks, 8192-wide layers), so those keep the barrier.
     const char *proto = getenv("HPNN_TP_PROTOCOL");
     long long local_doubles = 0;
     for (int l = 0; l < net->n_layers; ++l) local_doubles += (long long)net->rows[l] * net->ld[l];
-    bool tagged = net->world > 1 && local_doubles * 8 < (48LL << 20);
+    bool tagged = net->world > 1 && (local_doubles * 8 < (48LL << 20) || net->world >= 4);
     if (proto && !strcmp(proto, "barrier")) tagged = false;
     if (proto && !strcmp(proto, "tagged")) tagged = net->world > 1;
     p.tagged = tagged ? 1 : 0;
@@ -377,13 +409,22 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
   }
   p.max_ld = max_ld;
   p.max_rows = (max_rows + 7) & ~7;
-  const int grid = hpnn_dev_persistent_grid();
   int rowpart = 8;
   for (int l = 0; l < net->n_layers; ++l) {
     const int d = row_part_doubles(net->rows[l], grid);
     rowpart = d > rowpart ? d : rowpart;
   }
-  const size_t smem = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles + rowpart);
+  smem_plain = sizeof(double) * ((size_t)p.max_ld + p.max_rows + kRedDoubles + rowpart);
+  return 0;
+}
+
+int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
+                          hpnn_train_result *result_dev, void *stream) {
+  if (!net || !o) return -1;
+  KP p;
+  const int grid = hpnn_dev_persistent_grid();
+  size_t smem = 0;
+  if (build_kp(net, o, mode, result_dev, grid, p, smem) != 0) return -1;
   {
     const int rc = launch_lazy1_if_eligible(p, grid, stream);
     if (rc <= 0) {
@@ -422,6 +463,85 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
                                   (cudaStream_t)stream);
   if (e != cudaSuccess) {
     set_error("cudaLaunchCooperativeKernel(k_train_sample)", e);
+    return -1;
+  }
+  ++g_launches;
+  return 0;
+}
+
+int hpnn_dev_train_sample_vranks(const hpnn_dev_net *nets, int world, const hpnn_train_opts *o, int mode,
+                                 hpnn_train_result *const *results_dev, void *stream) {
+  if (!nets || !o || world < 1 || world > HPNN_MAX_WORLD) return -1;
+  int sms = hpnn_dev_persistent_grid();
+  const int G = sms / world;
+  if (G < 1) {
+    set_error_msg("hpnn_dev_train_sample_vranks: more ranks than SMs");
+    return -1;
+  }
+  KP kp[HPNN_MAX_WORLD];
+  memset((void *)kp, 0, sizeof(kp));
+  size_t smem = 0;
+  int lazy1 = -1;
+  for (int r = 0; r < world; ++r) {
+    if (nets[r].world != world || nets[r].rank != r) {
+      set_error_msg("hpnn_dev_train_sample_vranks: nets[r] must be rank r of `world`");
+      return -1;
+    }
+    size_t sm_r = 0;
+    KP base;
+    memset((void *)&base, 0, sizeof(base));
+    if (build_kp(nets + r, o, mode, results_dev ? results_dev[r] : nullptr, G, base, sm_r) != 0) return -1;
+    if (r > 0) base.trace = nullptr;  // one trace buffer: rank 0 writes it
+    KP pl;
+    size_t sm_l = 0;
+    const int el = prepare_lazy1(base, G, pl, sm_l) == 0 ? 1 : 0;
+    if (lazy1 < 0) lazy1 = el;
+    if (el != lazy1) {
+      set_error_msg("hpnn_dev_train_sample_vranks: ranks disagree on the trainer variant");
+      return -1;
+    }
+    kp[r] = el ? pl : base;
+    const size_t s_r = el ? sm_l : sm_r;
+    smem = s_r > smem ? s_r : smem;
+    if (kp[r].tagged != kp[0].tagged) {
+      set_error_msg("hpnn_dev_train_sample_vranks: ranks disagree on the protocol");
+      return -1;
+    }
+  }
+  if (smem + sizeof(KP) + 1024 > 227 * 1024) {
+    set_error_msg("hpnn_dev_train_sample_vranks: layer too wide for the virtual-rank launch");
+    return -2;
+  }
+  // parameter block of every rank in device memory (one buffer per device, created on first use)
+  static KP *pv_dev[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return -1;
+  cudaError_t e = cudaSuccess;
+  if (!pv_dev[dev]) e = cudaMalloc((void **)&pv_dev[dev], sizeof(KP) * HPNN_MAX_WORLD);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(pv_dev[dev], kp, sizeof(KP) * world, cudaMemcpyHostToDevice, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("hpnn_dev_train_sample_vranks: parameter upload", e);
+    return -1;
+  }
+  if (lazy1) {
+    const int rc = launch_lazy1_vranks(pv_dev[dev], world, G, kp[0].tagged != 0, smem, stream);
+    if (rc == 0) ++g_launches;
+    return rc;
+  }
+  const void *kfn = kp[0].tagged ? (const void *)k_train_sample_vranks<true> : (const void *)k_train_sample_vranks<false>;
+  e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(k_train_sample_vranks)", e);
+    return -1;
+  }
+  const KP *pv = pv_dev[dev];
+  int g = G;
+  void *args[] = {(void *)&pv, (void *)&g};
+  e = cudaLaunchCooperativeKernel(kfn, dim3(world * G), dim3(kThreads), args, smem, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("cudaLaunchCooperativeKernel(k_train_sample_vranks)", e);
     return -1;
   }
   ++g_launches;

@@ -108,6 +108,7 @@ def _declare(lib):
         "hpnn_enable_peer_access": (i, [i, i]),
         "hpnn_last_error": (C.c_char_p, []),
         "hpnn_dev_train_sample": (i, [C.POINTER(DevNet), C.POINTER(TrainOpts), i, vp, vp]),
+        "hpnn_dev_train_sample_vranks": (i, [C.POINTER(DevNet), i, C.POINTER(TrainOpts), i, C.POINTER(vp), vp]),
         "hpnn_dev_persistent_grid": (i, []),
         "hpnn_dev_set_persistent_grid": (None, [i]),
         "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),

@@ -42,7 +42,7 @@ def split_rows(n: int, rank: int, world: int):
 
 class HpnnNet:
     def __init__(self, kernel: Kernel, nn_type: int, device: Optional[torch.device] = None,
-                 momentum: bool = True, group=None):
+                 momentum: bool = True, group=None, virtual_rank: Optional[tuple] = None):
         if not torch.cuda.is_available():
             raise RuntimeError("HpnnNet needs a CUDA device (use the 'cpu' or 'torch' engine otherwise)")
         self.lib = N.load()
@@ -50,7 +50,12 @@ class HpnnNet:
         self.dims = list(kernel.dims)
         self.name = kernel.name
         self.group = group
-        if group is not None:
+        self.virtual = virtual_rank is not None
+        if self.virtual:
+            # (rank, world) of a row-split job whose ranks all live on THIS device
+            # (parallel/virtual.py links the arenas and launches every rank in one cooperative grid)
+            self.rank, self.world = int(virtual_rank[0]), int(virtual_rank[1])
+        elif group is not None:
             import torch.distributed as dist
             self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         else:
@@ -99,7 +104,7 @@ class HpnnNet:
         for q in range(N.MAX_WORLD):
             net.arena[q] = None
         net.arena[self.rank] = self._arena_ptr
-        if self.world > 1:
+        if self.world > 1 and not self.virtual:
             self._exchange_arenas()
         # ---- per-sample staging: pinned result ring + device result slots
         self._n_slots = 1024
@@ -133,7 +138,7 @@ class HpnnNet:
             return
         self._closed = True
         torch.cuda.synchronize(self.device)
-        if self.world > 1:
+        if self.world > 1 and not self.virtual:
             import torch.distributed as dist
             dist.barrier(group=self.group)
         for p in self._peer_ptrs:
@@ -144,7 +149,7 @@ class HpnnNet:
 
     def __del__(self):
         try:
-            if self.world == 1:
+            if self.world == 1 or self.virtual:
                 self.close()
         except Exception:
             pass

@@ -206,6 +206,10 @@ def make_engine(backend: str, kernel: Kernel, nn_type: int, train: int, **kw):
         from .parallel.logical import LogicalRanksEngine
         world = int(backend.split(":")[1]) if ":" in backend else kw.pop("world", 1)
         return LogicalRanksEngine(kernel, nn_type, train, world=world, **kw)
+    if backend.startswith("virtual"):  # "virtual:P": P ranks of the persistent kernel in one cooperative launch
+        from .parallel.virtual import VirtualRanksEngine
+        world = int(backend.split(":")[1]) if ":" in backend else kw.pop("world", 2)
+        return VirtualRanksEngine(kernel, nn_type, train, world=world, **kw)
     if backend.startswith("torch"):
         dev = kw.pop("device", None) or ("cuda" if backend == "torch-cuda" else "cpu")
         return TorchEngine(kernel, nn_type, train, device=dev, **kw)

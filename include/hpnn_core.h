@@ -215,6 +215,14 @@ const char *hpnn_last_error(void);
  * (the softmaxed / activated output lands at off_out).  Returns 0 on success. */
 int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
                           hpnn_train_result *result_dev, void *stream);
+/* Virtual ranks: the same training step for ALL `world` ranks of a row-split job in ONE cooperative
+ * launch on the current device (each rank gets SMs / world CTAs).  nets[r] is rank r's descriptor:
+ * own weight slice, own arena, own sync words, arena[q] = rank q's arena -- all on this device.
+ * For verifying the multi-rank protocols where one GPU is available (the reference's counterpart
+ * is the DEBUG build that fakes three GPUs on device 0, include/libhpnn/common.h:511-572);
+ * results_dev[r] may be NULL.  Not a performance path. */
+int hpnn_dev_train_sample_vranks(const hpnn_dev_net *nets, int world, const hpnn_train_opts *o, int mode,
+                                 hpnn_train_result *const *results_dev, void *stream);
 /* number of co-resident CTAs the persistent kernel will use on this device */
 int hpnn_dev_persistent_grid(void);
 /* set grid (CTAs) used by K-P: 0 = one per SM (default) */

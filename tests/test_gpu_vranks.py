@@ -1,0 +1,85 @@
+"""Multi-rank protocols of the persistent trainers on ONE GPU: P virtual ranks inside one
+cooperative launch (hpnn_dev_train_sample_vranks), checked against the CPU engine.
+
+Covers what tests/test_gpu_multi.py can only do on a multi-GPU box: the row partition, the
+all-gather / reduce-scatter by stores into the other ranks' arenas, the fence + flag barrier and
+the tagged {value, tag} hand-over, for the streaming kernel (K-P) and the row-panel
+deferred-update kernel (K-PL1)."""
+import numpy as np
+import pytest
+
+import hpnn_b200 as hp
+from hpnn_b200 import _native as N
+from hpnn_b200.trainer import CpuEngine, make_engine
+
+from conftest import make_problem
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("proto", ["barrier", "tagged"])
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("nn_type,train", [(N.TYPE_ANN, N.TRAIN_BP), (N.TYPE_SNN, N.TRAIN_BPM)])
+def test_streaming_trainer_on_virtual_ranks(monkeypatch, world, proto, nn_type, train):
+    monkeypatch.setenv("HPNN_TP_PROTOCOL", proto)
+    k, _ = hp.generate_kernel(21, 40, [37, 29], 6)
+    X, T = make_problem(nn_type, 40, (37, 29), 6, n_samples=3, seed=4)
+    kw = dict(max_iter=60, min_iter=70, delta=1e-300)
+    eng = make_engine(f"virtual:{world}", k, nn_type, train, **kw)
+    cpu = CpuEngine(k, nn_type, train, cuda_defaults=True, **kw)
+    for x, t in zip(X, T):
+        a, b = eng.train(x, t), cpu.train(x, t)
+        assert a.n_iter == b.n_iter == 61
+        assert abs(a.init_err - b.init_err) < 1e-12 and abs(a.last_err - b.last_err) < 1e-12
+    for wa, wb in zip(eng.kernel().weights, cpu.kernel().weights):
+        np.testing.assert_allclose(wa, wb, atol=1e-12)
+    np.testing.assert_allclose(eng.run(X[0]), cpu.run(X[0]), atol=1e-12)
+    eng.close()
+    cpu.close()
+
+
+@pytest.mark.parametrize("proto", ["barrier", "tagged"])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto):
+    """K-PL1 with several ranks: per-rank column-slice sums scattered to the owning rank, forward
+    results and partial dot products stored into every rank's arena; 19 iterations = two
+    write-back periods of 8 plus a partial one."""
+    monkeypatch.setenv("HPNN_TP_PROTOCOL", proto)
+    lib = N.load()
+    lib.hpnn_dev_set_lazy(8, 0)
+    lib.hpnn_dev_set_lazy_panel(1)
+    try:
+        for nn_type in (N.TYPE_ANN, N.TYPE_SNN):
+            n_in, hid, n_out = 40, (600, 300, 150), 12
+            k, _ = hp.generate_kernel(77, n_in, list(hid), n_out)
+            X, T = make_problem(nn_type, n_in, hid, n_out, n_samples=2, seed=3)
+            n_it = 19
+            kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
+            eng = make_engine(f"virtual:{world}", k, nn_type, N.TRAIN_BP, **kw)
+            assert eng.nets[0].net.hist_depth == 8 and eng.nets[0].net.panel_stride > 0
+            cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw)
+            for x, t in zip(X, T):
+                a, b = eng.train(x, t), cpu.train(x, t)
+                assert a.n_iter == b.n_iter == n_it
+                assert abs(a.init_err - b.init_err) < 1e-12 and abs(a.last_err - b.last_err) < 1e-11
+            for wa, wb in zip(eng.kernel().weights, cpu.kernel().weights):
+                np.testing.assert_allclose(wa, wb, atol=1e-11)
+            eng.close()
+            cpu.close()
+    finally:
+        lib.hpnn_dev_set_lazy(-1, -1)
+        lib.hpnn_dev_set_lazy_panel(-1)
+
+
+def test_convergent_loop_on_virtual_ranks_takes_the_same_exit():
+    """The data-dependent exit (dE <= 1e-6 and argmax == target) is taken redundantly by every
+    rank; VirtualRanksEngine.train raises if they disagree."""
+    k, _ = hp.generate_kernel(4242, 64, [48], 10)
+    X, T = make_problem(N.TYPE_ANN, 64, (48,), 10, n_samples=2, seed=5)
+    eng = make_engine("virtual:4", k, N.TYPE_ANN, N.TRAIN_BP, max_iter=3000)
+    cpu = CpuEngine(k, N.TYPE_ANN, N.TRAIN_BP, cuda_defaults=True, max_iter=3000)
+    for x, t in zip(X, T):
+        a, b = eng.train(x, t), cpu.train(x, t)
+        assert abs(a.n_iter - b.n_iter) <= max(3, b.n_iter // 100) and a.success == b.success
+    eng.close()
+    cpu.close()
