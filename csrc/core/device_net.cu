@@ -196,6 +196,42 @@ void hpnn_net_set_type(hpnn_net *n, int type) {
 }
 long long hpnn_net_device_bytes(const hpnn_net *n) { return n ? (long long)n->bytes_dev : 0; }
 
+// After an abandoned sample (hpnn_train_result.status != 0) or a failed launch: barrier counters,
+// flag words, abort words and launch ids are in an undefined state on every rank.  Bring them back to
+// the state of a fresh net so that the next call starts clean.
+static void net_reset_sync(hpnn_net *n) {
+  for (auto &r : n->ranks) {
+    cudaSetDevice(r.dev);
+    cudaStreamSynchronize(r.stream);
+    // the whole arena, not only the flag words: the launch id restarts from zero, so no {value, tag}
+    // pair of an earlier launch may survive (its tag could match a future one)
+    cudaMemsetAsync(r.sync, 0, 256 * sizeof(unsigned), r.stream);
+    cudaMemsetAsync(r.arena, 0, sizeof(double) * (size_t)r.net.arena_doubles, r.stream);
+    cudaStreamSynchronize(r.stream);
+  }
+  cudaSetDevice(n->ranks[0].dev);
+}
+
+// Raise the abort word of ranks [0, upto) from the host while their persistent kernels are running
+// (a side stream: the kernels occupy the ranks' own streams), then wait for them to leave.
+static void net_abort_running(hpnn_net *n, int upto) {
+  static const unsigned long long one = 1ull;
+  for (int g = 0; g < upto; ++g) {
+    auto &r = n->ranks[g];
+    cudaSetDevice(r.dev);
+    cudaStream_t side = nullptr;
+    if (cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking) != cudaSuccess) continue;
+    cudaMemcpyAsync(reinterpret_cast<unsigned long long *>(r.arena + r.net.off_flags) + HPNN_MAX_WORLD, &one, sizeof(one),
+                    cudaMemcpyHostToDevice, side);
+    cudaStreamSynchronize(side);
+    cudaStreamDestroy(side);
+  }
+  for (int g = 0; g < upto; ++g) {
+    cudaSetDevice(n->ranks[g].dev);
+    cudaStreamSynchronize(n->ranks[g].stream);
+  }
+}
+
 static int net_launch(hpnn_net *n, const hpnn_train_opts *o, int mode, const double *in, const double *target) {
   const int NL = (int)n->dims.size() - 1;
   const int n_in = n->dims[0], n_out = n->dims[NL];
@@ -211,9 +247,16 @@ static int net_launch(hpnn_net *n, const hpnn_train_opts *o, int mode, const dou
               "target H2D");
   }
   // one persistent kernel per GPU; they meet in the cross-GPU barriers
-  for (auto &r : n->ranks) {
+  for (int g = 0; g < (int)n->ranks.size(); ++g) {
+    auto &r = n->ranks[g];
     cudaSetDevice(r.dev);
-    if (hpnn_dev_train_sample(&r.net, o, mode, r.res, r.stream) != 0) return -1;
+    if (hpnn_dev_train_sample(&r.net, o, mode, r.res, r.stream) != 0) {
+      // the ranks launched so far are waiting for this one: tell them to leave instead of letting
+      // them spin until their time-out (the message of the failed launch is kept)
+      net_abort_running(n, g);
+      net_reset_sync(n);
+      return -1;
+    }
   }
   auto &r0 = n->ranks[0];
   cudaSetDevice(r0.dev);
@@ -226,6 +269,12 @@ static int net_launch(hpnn_net *n, const hpnn_train_opts *o, int mode, const dou
     NET_CHECK(cudaStreamSynchronize(r.stream), "hpnn_net sync");
   }
   cudaSetDevice(r0.dev);
+  if (n->pin_res->status != 0) {
+    net_reset_sync(n);
+    hpnn::set_error_msg("hpnn_net: the sample was abandoned: a wait for another CTA or GPU exceeded the spin time-out "
+                        "(hpnn_dev_set_spin_timeout_ms / HPNN_SPIN_TIMEOUT_MS)");
+    return -1;
+  }
   return 0;
 }
 

@@ -54,6 +54,22 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long
 __device__ __forceinline__ void st_relaxed_sys(unsigned long long *p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// {value, tag} pairs are moved with the SCALAR 128-bit type (PTX ISA 8.3, ld/st .b128): a vector
+// access (.v2.b64) is, in the memory model, two 64-bit accesses that merely share an instruction,
+// whereas a naturally aligned scalar access is single-copy atomic -- the property the tagged
+// hand-over rests on (a reader never sees a new tag with an old value).  SASS: STG.E.128 / LDG.E.128.
+__device__ __forceinline__ void st_b128_relaxed_sys(void *p, unsigned long long lo, unsigned long long hi) {
+  asm volatile("{\n\t.reg .b128 q;\n\tmov.b128 q, {%1, %2};\n\tst.relaxed.sys.global.b128 [%0], q;\n\t}" ::"l"(p), "l"(lo), "l"(hi) : "memory");
+}
+__device__ __forceinline__ void st_b128_relaxed_gpu(void *p, unsigned long long lo, unsigned long long hi) {
+  asm volatile("{\n\t.reg .b128 q;\n\tmov.b128 q, {%1, %2};\n\tst.relaxed.gpu.global.b128 [%0], q;\n\t}" ::"l"(p), "l"(lo), "l"(hi) : "memory");
+}
+__device__ __forceinline__ void ld_b128_relaxed_sys(const void *p, unsigned long long &lo, unsigned long long &hi) {
+  asm volatile("{\n\t.reg .b128 q;\n\tld.relaxed.sys.global.b128 q, [%2];\n\tmov.b128 {%0, %1}, q;\n\t}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void ld_b128_relaxed_gpu(const void *p, unsigned long long &lo, unsigned long long &hi) {
+  asm volatile("{\n\t.reg .b128 q;\n\tld.relaxed.gpu.global.b128 q, [%2];\n\tmov.b128 {%0, %1}, q;\n\t}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+}
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
@@ -155,9 +171,7 @@ struct Dst {
 __device__ __forceinline__ void dst_store(const Dst &dst, int r, double y) {
   for (int q = 0; q < dst.n; ++q) {
     if (dst.tag)
-      asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};" ::"l"(dst.p[q] + 2 * (size_t)r),
-                   "l"(__double_as_longlong(y)), "l"(dst.tag)
-                   : "memory");
+      st_b128_relaxed_sys(dst.p[q] + 2 * (size_t)r, (unsigned long long)__double_as_longlong(y), dst.tag);
     else
       stg_cg(dst.p[q] + r, y);
   }

@@ -9,6 +9,7 @@ namespace hpnn {
 constexpr int kMaxRsplit = 4;  // row parts of a column task (see phase_cols)
 constexpr int kLazyChunk = 8;  // update factors kept per row / column by the deferred-update trainer
 constexpr int kLazyDotSlots = 160;  // per-CTA partial dot product slots per rank (>= grid size)
+constexpr size_t kMaxDynSmem = 226 * 1024;  // dynamic shared memory per CTA (227 KB minus the static variables)
 constexpr long long kLazyMinBytes = 64LL << 20;  // local weights of layers >= 1 below this: not worth it
 
 struct KP {
@@ -23,7 +24,91 @@ struct KP {
   hpnn_train_result *result;
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
+  int fault;  // fault injection (tests): 1 = this rank leaves at kernel entry, as if its launch had failed
+  unsigned long long spin_budget_ns;  // longest time any wait may take before the job is abandoned (0 = unbounded)
 };
+
+// ---- bounded waiting --------------------------------------------------------------------------
+// Every wait in the persistent kernels (grid barrier, cross-rank flags, tagged pairs) is a spin on
+// memory somebody else writes.  If that somebody never comes -- a rank whose launch failed, a peer
+// process that died -- the reference at least exits (CUDA_* macros call exit(-1),
+// include/libhpnn/common.h:337-353); an unbounded spin would hang every GPU of the job.  So:
+//   * each rank has an ABORT word in its arena (behind the barrier flags, so peers can write it);
+//   * a spinning thread looks at the clock every 1024 polls; when one wait has lasted longer than
+//     spin_budget_ns it raises the abort word of EVERY rank and leaves the loop;
+//   * the same slow path looks at the local abort word, so all other waits end within 1024 polls;
+//   * the iteration loop tests the word once per iteration (loaded at the start of the iteration,
+//     consumed at its end: off the critical path) and leaves; hpnn_train_result.status = 1.
+// After an abort the weights, the barrier words and the tags of that sample are meaningless; the
+// host reports the error and must reset the sync state (hpnn_net does, HpnnNet.reset_sync()).
+constexpr int kAbortSlot = HPNN_MAX_WORLD;  // u64 index of the abort word in the arena's flag area
+struct WatchState {
+  unsigned long long *abort_word[HPNN_MAX_WORLD];  // [rank] is the local one
+  int rank, world;
+  unsigned long long budget_ns;
+  unsigned tripped;   // a thread of this CTA gave up or saw the abort word
+  unsigned exit_now;  // CTA-uniform copy, written by thread 0 once per iteration
+};
+static __shared__ WatchState s_watch;
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void watch_init(const KP &p) {
+  if (threadIdx.x == 0) {
+    const hpnn_dev_net &n = p.net;
+    for (int q = 0; q < HPNN_MAX_WORLD; ++q)
+      s_watch.abort_word[q] =
+          q < n.world ? reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + kAbortSlot : nullptr;
+    s_watch.rank = n.rank;
+    s_watch.world = n.world;
+    s_watch.budget_ns = p.spin_budget_ns;
+    s_watch.tripped = 0;
+    s_watch.exit_now = 0;
+  }
+  __syncthreads();
+}
+// slow path of a spin: true = stop waiting
+static __device__ __noinline__ bool spin_check(unsigned long long &t0) {
+  if (s_watch.tripped) return true;
+  if (ld_relaxed_sys(s_watch.abort_word[s_watch.rank]) != 0ull) {
+    s_watch.tripped = 1;
+    return true;
+  }
+  if (s_watch.budget_ns == 0ull) return false;
+  const unsigned long long now = global_ns();
+  if (t0 == 0ull) {
+    t0 = now;
+    return false;
+  }
+  if (now - t0 <= s_watch.budget_ns) return false;
+  for (int q = 0; q < s_watch.world; ++q) st_relaxed_sys(s_watch.abort_word[q], 1ull);
+  s_watch.tripped = 1;
+  return true;
+}
+struct Spin {
+  unsigned n = 0;
+  unsigned long long t0 = 0;
+  // call after every poll that did not succeed
+  __device__ __forceinline__ bool give_up() {
+    if ((++n & 1023u) != 0u) return false;
+    return spin_check(t0);
+  }
+};
+// once per iteration: thread 0 passes the abort word it loaded at the START of the iteration
+// (`seen`); call before a phase that ends in __syncthreads, read s_watch.exit_now after it
+__device__ __forceinline__ void watch_publish(unsigned long long seen) {
+  if (threadIdx.x == 0) s_watch.exit_now = (seen != 0ull || s_watch.tripped) ? 1u : 0u;
+}
+// for hpnn_train_result.status (thread 0 of CTA 0, at the very end)
+__device__ __forceinline__ int watch_status() {
+  return (s_watch.tripped || s_watch.exit_now || ld_relaxed_sys(s_watch.abort_word[s_watch.rank]) != 0ull) ? 1 : 0;
+}
+__device__ __forceinline__ unsigned long long watch_peek() {
+  return threadIdx.x == 0 ? ld_relaxed_sys(s_watch.abort_word[s_watch.rank]) : 0ull;
+}
 
 // Grid barrier, extended to all ranks when world > 1.
 //
@@ -58,7 +143,9 @@ struct Barrier {
       unsigned *prev = sync + 32 * ((k + 2u) % 3u);
       ++k;
       red_add_release_gpu(c, 1u);
+      Spin sp;
       while (ld_relaxed_gpu(c) != grid) {
+        if (sp.give_up()) break;
       }
       if (bid == 0) *prev = 0;
       fence_gpu();
@@ -78,13 +165,16 @@ struct Barrier {
       ++k;
       if (n.world > 1 && remote) fence_sys();  // peer stores performed before the arrive
       red_add_release_gpu(c, 1u);
+      Spin sp;
       if (n.world == 1) {
         while (ld_relaxed_gpu(c) != grid) {
+          if (sp.give_up()) break;
         }
         if (bid == 0) *prev = 0;
         fence_gpu();
       } else if (bid == 0) {
         while (ld_relaxed_gpu(c) != grid) {
+          if (sp.give_up()) break;
         }
         *prev = 0;
         const unsigned long long we = (unsigned long long)k;
@@ -98,12 +188,14 @@ struct Barrier {
         for (int q = 0; q < n.world; ++q) {
           if (q == n.rank) continue;
           while (ld_relaxed_sys(mine + q) < we) {
+            if (sp.give_up()) break;
           }
         }
         fence_sys();  // acquire: the peers' stores into this arena are visible after it
         st_release_gpu(sync + 96, k);
       } else {
         while (ld_relaxed_gpu(sync + 96) != k) {
+          if (sp.give_up()) break;
         }
         fence_gpu();
       }
@@ -113,7 +205,7 @@ struct Barrier {
 };
 
 // ---- tagged hand-over: every value another CTA (or GPU) waits for travels as a 16-byte
-// {value, tag} pair written with ONE 128-bit store; the consumer spins on the pair itself until
+// {value, tag} pair written with ONE scalar 128-bit store (st.b128, see dev_common.cuh); the consumer spins on the pair itself until
 // the tag is the one it expects.  Data and "ready" flag arrive in the same access, so a phase
 // boundary costs one write + one read round trip instead of a barrier plus a staging pass, and
 // across GPUs no system-scope fence is needed at all (measured: a fence-based cross-GPU barrier
@@ -122,10 +214,8 @@ struct Barrier {
 // SYS selects system scope (peer memory) instead of GPU scope.
 template <bool SYS>
 __device__ __forceinline__ void st_pair(double *base, long long idx, double v, unsigned long long tag) {
-  if (SYS)
-    asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};" ::"l"(base + 2 * idx), "l"(__double_as_longlong(v)), "l"(tag) : "memory");
-  else
-    asm volatile("st.relaxed.gpu.global.v2.b64 [%0], {%1, %2};" ::"l"(base + 2 * idx), "l"(__double_as_longlong(v)), "l"(tag) : "memory");
+  if (SYS) st_b128_relaxed_sys(base + 2 * idx, (unsigned long long)__double_as_longlong(v), tag);
+  else st_b128_relaxed_gpu(base + 2 * idx, (unsigned long long)__double_as_longlong(v), tag);
 }
 #ifndef HPNN_POLL_BACKOFF_NS
 #define HPNN_POLL_BACKOFF_NS 0  /* measured: any back-off only adds latency (20.1 -> 24.2 us/iteration at 64 ns) */
@@ -144,29 +234,29 @@ __device__ __forceinline__ void ld_pairs_wait(const double *const (&addr)[U], co
     v[u] = 0.0;
   }
   bool all;
+  Spin sp;
   do {
-    long long a[U];
+    unsigned long long a[U];
     unsigned long long t[U];
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (!done[u]) {
-        if (SYS)
-          asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(a[u]), "=l"(t[u]) : "l"(addr[u]) : "memory");
-        else
-          asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(a[u]), "=l"(t[u]) : "l"(addr[u]) : "memory");
+        if (SYS) ld_b128_relaxed_sys(addr[u], a[u], t[u]);
+        else ld_b128_relaxed_gpu(addr[u], a[u], t[u]);
       }
     all = true;
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (!done[u]) {
         if (t[u] == tag) {
-          v[u] = __longlong_as_double(a[u]);
+          v[u] = __longlong_as_double((long long)a[u]);
           done[u] = true;
         } else {
           all = false;
         }
       }
     if (kPollBackoffNs && !all) __nanosleep(kPollBackoffNs);
+    if (!all && sp.give_up()) break;  // abandoned job: the values are meaningless from here on
   } while (!all);
 }
 template <bool SYS>

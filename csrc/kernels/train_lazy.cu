@@ -286,6 +286,8 @@ __device__ __forceinline__ void phase_rows_lazy(double *W, int ld, int rows, con
 
 __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_constant__ KP p) {
   extern __shared__ double smem[];
+  watch_init(p);
+  if (p.fault == 1) return;  // injected fault: this rank never shows up
   // xs doubles as the factor staging area of the write-back pass (the top-down phases read their
   // input vector from global memory), so it is at least kFlushStageDoubles long.  Keeping the
   // footprint at the plain trainer's size matters: 64 KB more shared memory shrank L1 enough to
@@ -362,6 +364,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_
   for (;;) {
     ++iter;
     trace(1);
+    const unsigned long long abort_seen = watch_peek();
     const bool flush = (m + 1 >= depth);
     // ---- top-down: partial W_true^T.delta (read-only unless this is a write-back iteration)
     for (int l = last; l >= 1; --l) {
@@ -414,9 +417,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_
       trace(400 + l);
     }
     cur ^= 1;
+    watch_publish(abort_seen);
     st = output_stats(p.type, p.stable, act_of(n.rank, NL, cur), target, n_out, n.row0[last], n.rows[last], ds, nullptr,
                       red);
     trace(2);
+    if (s_watch.exit_now) break;  // the job was abandoned (a wait ran out of time)
     dE = E - st.err;
     E = st.err;
     ok = (st.argmax == st.target);
@@ -449,7 +454,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_
     r.n_iter = iter;
     r.first_ok = first_ok;
     r.success = ok;
-    r.reserved = st.argmax;
+    r.status = watch_status();
     *p.result = r;
   }
 }

@@ -387,6 +387,8 @@ __device__ __forceinline__ void gather_dots_tagged(const hpnn_dev_net &n, int l,
 template <bool TG>
 __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int grid, const int b) {
   extern __shared__ double smem[];
+  watch_init(p);
+  if (p.fault == 1) return;  // injected fault: this rank never shows up
   const hpnn_dev_net &n = p.net;
   const int NL = n.n_layers;
   const int pmax = p.max_rows;  // here: widest panel, padded to 8 (see the launcher)
@@ -516,6 +518,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   for (;;) {
     ++iter;
     trace(1);
+    const unsigned long long abort_seen = watch_peek();
     const unsigned long long tag = tag_of(iter);
     const bool flush = (m + 1 >= depth);
     // ---- top-down
@@ -653,8 +656,10 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
       trace(400 + l);
     }
     cur ^= 1;
+    watch_publish(abort_seen);
     st = evaluate(tag, out_row0, plast.cnt, dsl, nullptr);
     trace(2);
+    if (s_watch.exit_now) break;  // the job was abandoned (a wait ran out of time)
     dE = E - st.err;
     E = st.err;
     ok = (st.argmax == st.target);
@@ -702,7 +707,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     r.n_iter = iter;
     r.first_ok = first_ok;
     r.success = ok;
-    r.reserved = st.argmax;
+    r.status = watch_status();
     *p.result = r;
   }
 }
@@ -759,7 +764,7 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
   rowpart = pmax * kZStride;
   p.max_rows = pmax;  // the kernel's carve-up uses the panel height, not the layer height
   const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart);
-  if (smem > 227 * 1024) return 1;
+  if (smem > kMaxDynSmem) return 1;
   p_out = p;
   smem_out = smem;
   return 0;

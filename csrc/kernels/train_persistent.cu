@@ -29,6 +29,8 @@ namespace hpnn {
 template <bool TG>
 __device__ __forceinline__ void train_sample_body(const KP &p, const int grid, const int bid) {
   extern __shared__ double smem[];
+  watch_init(p);
+  if (p.fault == 1) return;  // injected fault: this rank never shows up
   double *xs = smem;
   double *ds = xs + p.max_ld;
   double *red = ds + p.max_rows;
@@ -123,6 +125,7 @@ __device__ __forceinline__ void train_sample_body(const KP &p, const int grid, c
     for (;;) {
       ++iter;
       trace(1);
+      const unsigned long long abort_seen = watch_peek();
       const unsigned long long tag = tag_of(iter);
       // ---- top-down: deltas from the old weights fused with the update
       for (int l = last; l >= 1; --l) {
@@ -172,8 +175,10 @@ __device__ __forceinline__ void train_sample_body(const KP &p, const int grid, c
       }
       cur ^= 1;
       // ---- evaluate (every CTA, identical arithmetic => identical decision)
+      watch_publish(abort_seen);
       st = evaluate(tag, n.row0[last], n.rows[last], ds, nullptr);
       trace(2);
+      if (s_watch.exit_now) break;  // the job was abandoned (a wait ran out of time)
       dE = E - st.err;
       E = st.err;
       ok = (st.argmax == st.target);
@@ -195,7 +200,7 @@ __device__ __forceinline__ void train_sample_body(const KP &p, const int grid, c
     r.n_iter = iter;
     r.first_ok = first_ok;
     r.success = ok;
-    r.reserved = st.argmax;
+    r.status = watch_status();
     *p.result = r;
   }
 }
@@ -238,6 +243,8 @@ extern long long g_lazy_min_bytes;
 
 // ------------------------------- host side ---------------------------------
 static int g_grid_override = 0;
+static long long g_spin_timeout_ms = -1;  // -1: HPNN_SPIN_TIMEOUT_MS or 10 s
+static int g_fault_kind = 0, g_fault_rank = -1;
 static long long *g_trace = nullptr;
 static int g_trace_cap = 0;
 static thread_local char g_err[512] = "";
@@ -273,6 +280,13 @@ long long hpnn_abi_sizeof(int which) {
 }
 
 void hpnn_dev_set_persistent_grid(int ctas) { g_grid_override = ctas; }
+
+void hpnn_dev_set_spin_timeout_ms(long long ms) { g_spin_timeout_ms = ms; }
+
+void hpnn_dev_set_fault(int kind, int rank) {
+  g_fault_kind = kind;
+  g_fault_rank = rank;
+}
 
 void hpnn_dev_set_phase_trace(long long *dev_buf, int capacity_pairs) {
   g_trace = dev_buf;
@@ -396,6 +410,15 @@ static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
   }
   p.lazy_depth = 0;
   p.prefetch_bytes = 0;
+  {
+    static const long long env_ms = [] {
+      const char *e = getenv("HPNN_SPIN_TIMEOUT_MS");
+      return e ? atoll(e) : 10000LL;
+    }();
+    const long long ms = g_spin_timeout_ms >= 0 ? g_spin_timeout_ms : env_ms;
+    p.spin_budget_ns = ms > 0 ? (unsigned long long)ms * 1000000ull : 0ull;
+    p.fault = (g_fault_kind == 1 && g_fault_rank == net->rank) ? 1 : 0;
+  }
   p.trace = g_trace;
   p.trace_cap = g_trace_cap;
   int max_ld = 8, max_rows = 8;
@@ -432,7 +455,7 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
       return rc;
     }
   }
-  if (smem <= 227 * 1024) {
+  if (smem <= kMaxDynSmem) {
     // BP on layers far larger than L2: deferred rank-1 updates save most of the write-back traffic
     const int rc = launch_lazy_if_eligible(p, grid, smem, stream);
     if (rc <= 0) {
@@ -448,7 +471,7 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
       return rc;
     }
   }
-  if (smem > 227 * 1024) {
+  if (smem > kMaxDynSmem) {
     set_error_msg("hpnn_dev_train_sample: layer too wide for the persistent kernel (use the multi-launch path)");
     return -2;
   }
@@ -508,7 +531,7 @@ int hpnn_dev_train_sample_vranks(const hpnn_dev_net *nets, int world, const hpnn
       return -1;
     }
   }
-  if (smem + sizeof(KP) + 1024 > 227 * 1024) {
+  if (smem + sizeof(KP) > kMaxDynSmem) {
     set_error_msg("hpnn_dev_train_sample_vranks: layer too wide for the virtual-rank launch");
     return -2;
   }

@@ -82,6 +82,7 @@ __device__ __forceinline__ double smem_row(double *wrow, double *mrow, const dou
 __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __grid_constant__ RP rp) {
   extern __shared__ double smem[];
   const KP &p = rp.kp;
+  watch_init(p);
   const hpnn_dev_net &n = p.net;
   const int NL = n.n_layers, grid = gridDim.x, b = blockIdx.x;
   const int n_out = n.dims[NL];
@@ -209,6 +210,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
     for (;;) {
       ++iter;
       trace(1);
+      const unsigned long long abort_seen = watch_peek();
       const unsigned long long tag = tag_of(iter);
       // owned deltas of the output layer
       for (int i = threadIdx.x; i < s_cnt[last]; i += blockDim.x) down[s_doff[last] + i] = dout[s_first[last] + i * grid];
@@ -282,8 +284,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
       }
       // ---- bottom-up: layer 0 update fused with its forward, then the rest
       forward_all(tag, upd);
+      watch_publish(abort_seen);
       st = output_stats<true>(p.type, p.stable, zout, target, n_out, 0, n_out, dout, nullptr, red);
       trace(2);
+      if (s_watch.exit_now) break;  // the job was abandoned (a wait ran out of time)
       dE = E - st.err;
       E = st.err;
       ok = (st.argmax == st.target);
@@ -314,7 +318,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_resident(const __g
       r.n_iter = iter;
       r.first_ok = first_ok;
       r.success = ok;
-      r.reserved = st.argmax;
+      r.status = watch_status();
       *p.result = r;
     }
   }

@@ -19,7 +19,7 @@ _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libhpnn_core.so"
 
 class TrainResult(C.Structure):
     _fields_ = [("init_err", C.c_double), ("final_de", C.c_double), ("last_err", C.c_double),
-                ("n_iter", C.c_int), ("first_ok", C.c_int), ("success", C.c_int), ("reserved", C.c_int)]
+                ("n_iter", C.c_int), ("first_ok", C.c_int), ("success", C.c_int), ("status", C.c_int)]
 
 
 class TrainOpts(C.Structure):
@@ -109,6 +109,8 @@ def _declare(lib):
         "hpnn_last_error": (C.c_char_p, []),
         "hpnn_dev_train_sample": (i, [C.POINTER(DevNet), C.POINTER(TrainOpts), i, vp, vp]),
         "hpnn_dev_train_sample_vranks": (i, [C.POINTER(DevNet), i, C.POINTER(TrainOpts), i, C.POINTER(vp), vp]),
+        "hpnn_dev_set_spin_timeout_ms": (None, [ll]),
+        "hpnn_dev_set_fault": (None, [i, i]),
         "hpnn_dev_persistent_grid": (i, []),
         "hpnn_dev_set_persistent_grid": (None, [i]),
         "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),

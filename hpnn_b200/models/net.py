@@ -218,8 +218,24 @@ class HpnnNet:
         self._res_host[:nd].copy_(self._res_dev[:nd], non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         buf = self._res_host.numpy()
-        arr = (N.TrainResult * n).from_buffer_copy(buf[:nd].tobytes())
-        return list(arr)
+        arr = list((N.TrainResult * n).from_buffer_copy(buf[:nd].tobytes()))
+        if any(r.status != 0 for r in arr):
+            # a wait inside the persistent kernel ran out of time (a rank that never launched, a dead
+            # peer): every rank left its kernel; weights and sync words of this net are undefined now
+            self.reset_sync()
+            raise RuntimeError("hpnn_b200: sample abandoned, a wait for another CTA or GPU exceeded the spin "
+                               "time-out (hpnn_dev_set_spin_timeout_ms / HPNN_SPIN_TIMEOUT_MS)")
+        return arr
+
+    def reset_sync(self) -> None:
+        """Barrier counters, flag words, abort word and launch id back to the state of a fresh net
+        (after an abandoned sample; every rank of the job must do this before the next launch).
+        The whole arena is cleared: the launch id restarts from zero, so no {value, tag} pair of an
+        earlier launch may survive (its tag could match a future one)."""
+        torch.cuda.synchronize(self.device)
+        self.lib.hpnn_dev_memset(self._sync_ptr, 0, 256 * 4, self._stream())
+        self.arena.zero_()
+        torch.cuda.synchronize(self.device)
 
     def train_sample(self, x: torch.Tensor, t: torch.Tensor, opts: N.TrainOpts) -> N.TrainResult:
         self.load_sample(x, t)

@@ -66,6 +66,12 @@ class VirtualRanksEngine:
         torch.cuda.synchronize(self.device)
         raw = self._res.cpu().numpy()
         results = [N.TrainResult.from_buffer_copy(raw[r].tobytes()) for r in range(self.world)]
+        if any(r.status != 0 for r in results):
+            self.last_status = [r.status for r in results]
+            for n in self.nets:
+                n.reset_sync()
+            raise RuntimeError("hpnn_b200: sample abandoned on ranks %s (spin time-out)" %
+                               [i for i, r in enumerate(results) if r.status != 0])
         first = results[0]
         for r in results[1:]:  # every rank takes the exit decision redundantly: they must agree
             if (r.n_iter, r.success, r.first_ok) != (first.n_iter, first.success, first.first_ok):

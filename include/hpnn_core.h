@@ -101,7 +101,8 @@ typedef struct {
   int n_iter;       /* N_ITER                                               */
   int first_ok;     /* argmax matched the target after iteration 1 (OK/NO)  */
   int success;      /* loop-exit is_ok (SUCCESS!/FAIL!)                      */
-  int reserved;
+  int status;       /* device engine: 0 = ran to completion, 1 = abandoned (a wait for another CTA or
+                     * rank exceeded the spin time-out: weights and numbers above are meaningless)     */
 } hpnn_train_result;
 
 typedef struct {
@@ -223,6 +224,15 @@ int hpnn_dev_train_sample(const hpnn_dev_net *net, const hpnn_train_opts *o, int
  * results_dev[r] may be NULL.  Not a performance path. */
 int hpnn_dev_train_sample_vranks(const hpnn_dev_net *nets, int world, const hpnn_train_opts *o, int mode,
                                  hpnn_train_result *const *results_dev, void *stream);
+/* Longest time any single wait inside the persistent kernels (grid barrier, cross-rank flag, tagged
+ * pair) may last before the whole job is abandoned: every rank leaves its kernel and reports
+ * hpnn_train_result.status = 1 instead of hanging (a rank whose launch failed, a dead peer process).
+ * ms < 0: default (HPNN_SPIN_TIMEOUT_MS, else 10 000); 0: never give up.  The reference has no such
+ * wait: it synchronises through the host and exits on any CUDA error (include/libhpnn/common.h:337-353). */
+void hpnn_dev_set_spin_timeout_ms(long long ms);
+/* Fault injection for tests: kind 1 = the kernels launched for rank `rank` return at once, as if that
+ * rank's launch had failed; kind 0 = off. */
+void hpnn_dev_set_fault(int kind, int rank);
 /* number of co-resident CTAs the persistent kernel will use on this device */
 int hpnn_dev_persistent_grid(void);
 /* set grid (CTAs) used by K-P: 0 = one per SM (default) */

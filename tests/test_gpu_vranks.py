@@ -83,3 +83,40 @@ def test_convergent_loop_on_virtual_ranks_takes_the_same_exit():
         assert abs(a.n_iter - b.n_iter) <= max(3, b.n_iter // 100) and a.success == b.success
     eng.close()
     cpu.close()
+
+
+@pytest.mark.parametrize("proto", ["barrier", "tagged"])
+def test_missing_rank_is_reported_not_waited_for(monkeypatch, proto):
+    """Fault injection: one rank of four never shows up (its CTAs leave at kernel entry, as after a
+    failed launch).  Every other rank must give up within the spin time-out and say so in
+    hpnn_train_result.status; the call returns an error in well under two seconds, and the same
+    engine works again afterwards."""
+    import time
+
+    monkeypatch.setenv("HPNN_TP_PROTOCOL", proto)
+    lib = N.load()
+    k, _ = hp.generate_kernel(21, 40, [37, 29], 6)
+    X, T = make_problem(N.TYPE_ANN, 40, (37, 29), 6, n_samples=1, seed=4)
+    kw = dict(max_iter=60, min_iter=70, delta=1e-300)
+    eng = make_engine("virtual:4", k, N.TYPE_ANN, N.TRAIN_BP, **kw)
+    eng.train(X[0], T[0])  # warm: module load, first launch
+    lib.hpnn_dev_set_spin_timeout_ms(200)
+    lib.hpnn_dev_set_fault(1, 2)
+    try:
+        t0 = time.perf_counter()
+        with pytest.raises(RuntimeError, match="abandoned"):
+            eng.train(X[0], T[0])
+        assert time.perf_counter() - t0 < 2.0
+        # ranks 0, 1 and 3 ran and gave up; rank 2 never wrote its result slot
+        assert [eng.last_status[r] for r in (0, 1, 3)] == [1, 1, 1]
+    finally:
+        lib.hpnn_dev_set_fault(0, -1)
+        lib.hpnn_dev_set_spin_timeout_ms(-1)
+    # the engine is usable again (weights were garbage-updated by the abandoned sample: reload them)
+    for n in eng.nets:
+        n.load_weights(k)
+    cpu = CpuEngine(k, N.TYPE_ANN, N.TRAIN_BP, cuda_defaults=True, **kw)
+    a, b = eng.train(X[0], T[0]), cpu.train(X[0], T[0])
+    assert a.n_iter == b.n_iter and abs(a.last_err - b.last_err) < 1e-12
+    eng.close()
+    cpu.close()
