@@ -6,6 +6,7 @@
 // (single process, src/libhpnn.c:201-305), minus its "everything lives on GPU 0" layout.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -32,6 +33,7 @@ struct hpnn_net {
     cudaStream_t stream = nullptr;
   };
   std::vector<Rank> ranks;
+  hpnn_symm *symm = nullptr;  // several GPUs: the arenas are one symmetric set (multicast when the fabric has NVLS)
   double *pin = nullptr;  // pinned staging: input | target | output
   hpnn_train_result *pin_res = nullptr;
   size_t bytes_dev = 0;
@@ -58,11 +60,12 @@ void hpnn_net_destroy(hpnn_net *n) {
     if (r.stream) cudaStreamSynchronize(r.stream);
     for (double *p : r.W) cudaFree(p);
     for (double *p : r.dW) cudaFree(p);
-    cudaFree(r.arena);
+    if (!n->symm) cudaFree(r.arena);
     cudaFree(r.sync);
     cudaFree(r.res);
     if (r.stream) cudaStreamDestroy(r.stream);
   }
+  if (n->symm) hpnn_symm_destroy(n->symm);
   if (n->pin) cudaFreeHost(n->pin);
   if (n->pin_res) cudaFreeHost(n->pin_res);
   if (n->bx) cudaFree(n->bx);
@@ -163,16 +166,36 @@ hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gp
       r.net.dW[l] = r.dW[l];
       n->bytes_dev += bytes * (n->momentum ? 2 : 1);
     }
-    r.arena = (double *)hpnn_dev_alloc(sizeof(double) * (size_t)doubles);
     r.sync = (unsigned *)hpnn_dev_alloc(256 * sizeof(unsigned));
     r.res = (hpnn_train_result *)hpnn_dev_alloc(sizeof(hpnn_train_result));
     n->bytes_dev += sizeof(double) * (size_t)doubles;
-    ok = ok && r.arena && r.sync && r.res && cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && r.sync && r.res && cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) == cudaSuccess;
     r.net.local_sync = r.sync;
   }
   if (ok) {
-    for (auto &r : n->ranks)
+    // arenas: the same layout on every rank (hpnn_dev_arena_layout does not depend on the rank's
+    // row counts).  Several GPUs: one symmetric set, so that the kernels can also reach all copies
+    // through the multicast address; plain allocations if the VMM path is unavailable.
+    const size_t arena_bytes = sizeof(double) * (size_t)n->ranks[0].net.arena_doubles;
+    const char *no_symm = getenv("HPNN_SYMM");
+    if (n_gpus > 1 && !(no_symm && !strcmp(no_symm, "ipc"))) {
+      int devs[HPNN_MAX_WORLD];
+      for (int g = 0; g < n_gpus; ++g) devs[g] = n->ranks[g].dev;
+      const char *no_mc = getenv("HPNN_MULTICAST");
+      n->symm = hpnn_symm_create_local(devs, n_gpus, arena_bytes, !(no_mc && !strcmp(no_mc, "0")));
+    }
+    for (int g = 0; g < n_gpus && ok; ++g) {
+      auto &r = n->ranks[g];
+      cudaSetDevice(r.dev);
+      r.arena = n->symm ? (double *)hpnn_symm_ptr(n->symm, g) : (double *)hpnn_dev_alloc(arena_bytes);
+      ok = r.arena != nullptr;
+    }
+  }
+  if (ok) {
+    for (auto &r : n->ranks) {
       for (int q = 0; q < n_gpus; ++q) r.net.arena[q] = n->ranks[q].arena;
+      r.net.arena_mc = n->symm ? (double *)hpnn_symm_mc_ptr(n->symm) : nullptr;
+    }
     const size_t pin_doubles = (size_t)k->dims[0] + 2 * (size_t)k->dims[NL];
     ok = cudaMallocHost((void **)&n->pin, sizeof(double) * pin_doubles) == cudaSuccess &&
          cudaMallocHost((void **)&n->pin_res, sizeof(hpnn_train_result)) == cudaSuccess;

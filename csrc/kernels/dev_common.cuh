@@ -70,6 +70,23 @@ __device__ __forceinline__ void ld_b128_relaxed_sys(const void *p, unsigned long
 __device__ __forceinline__ void ld_b128_relaxed_gpu(const void *p, unsigned long long &lo, unsigned long long &hi) {
   asm volatile("{\n\t.reg .b128 q;\n\tld.relaxed.gpu.global.b128 q, [%2];\n\tmov.b128 {%0, %1}, q;\n\t}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
 }
+// NVLS: one store to the multicast address of a symmetric allocation (hpnn_symm_mc_ptr) is replicated
+// by the NVSwitch into every rank's copy; a reduction is applied to every copy; a load-reduce returns
+// the sum over the copies.  The address decides the routing (SASS shows plain STG / REDG / LDGMC).
+__device__ __forceinline__ void multimem_st_f64(double *mc, double v) {
+  asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(mc), "d"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st_u64(unsigned long long *mc, unsigned long long v) {
+  asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_f64(double *mc, double v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.f64 [%0], %1;" ::"l"(mc), "d"(v) : "memory");
+}
+__device__ __forceinline__ double multimem_ld_reduce_add_f64(const double *mc) {
+  double v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(v) : "l"(mc) : "memory");
+  return v;
+}
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
@@ -167,8 +184,13 @@ struct Dst {
   double *p[HPNN_MAX_WORLD];
   int n;
   unsigned long long tag;  // != 0: publish {value, tag} pairs (tagged hand-over, see kp_common.cuh)
+  double *mc;              // != nullptr (plain buffers only): the same offset at the multicast address
 };
 __device__ __forceinline__ void dst_store(const Dst &dst, int r, double y) {
+  if (!dst.tag && dst.mc) {  // all-gather in ONE store: the switch writes every rank's copy
+    multimem_st_f64(dst.mc + r, y);
+    return;
+  }
   for (int q = 0; q < dst.n; ++q) {
     if (dst.tag)
       st_b128_relaxed_sys(dst.p[q] + 2 * (size_t)r, (unsigned long long)__double_as_longlong(y), dst.tag);

@@ -179,10 +179,14 @@ struct Barrier {
         *prev = 0;
         const unsigned long long we = (unsigned long long)k;
         fence_sys();  // release: everything this rank wrote is visible before the flags
-        for (int q = 0; q < n.world; ++q) {
-          if (q == n.rank) continue;
-          unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
-          st_relaxed_sys(f, we);
+        if (n.arena_mc) {  // one multicast store sets this rank's flag word on every rank
+          multimem_st_u64(reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags) + n.rank, we);
+        } else {
+          for (int q = 0; q < n.world; ++q) {
+            if (q == n.rank) continue;
+            unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
+            st_relaxed_sys(f, we);
+          }
         }
         const unsigned long long *mine = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
         for (int q = 0; q < n.world; ++q) {

@@ -74,6 +74,7 @@ struct DotOut {
   const double *HV;  // factor chunks of the next layer, indexed by the global row of this layer
   int row0;
   unsigned long long tag;  // != 0: publish the chunk as 8 {value, tag} pairs (tagged hand-over)
+  double *mc;              // plain chunks only: the slot at the multicast address (one store reaches all ranks)
 };
 
 

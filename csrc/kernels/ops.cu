@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   Dst dst;
   dst.n = 1;
   dst.tag = 0;
+  dst.mc = nullptr;
   dst.p[0] = y;
   phase_rows<UPD>(W, dW, ld, rows, xs, ds, lr, alpha, act_kind, dst, pick_row_segments(rows, ld, gridDim.x), rowpart, gridDim.x, blockIdx.x);
 }

@@ -329,10 +329,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_
     Dst dst;
     dst.n = n.world;
     dst.tag = 0ull;
+    dst.mc = nullptr;
     for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + (size_t)n.row0[l];
     DotOut dots;
     dots.n = n.world;
     dots.tag = 0ull;
+    dots.mc = nullptr;
     dots.p[0] = nullptr;
     if (l + 1 < NL && m > 0) {
       for (int q = 0; q < n.world; ++q)

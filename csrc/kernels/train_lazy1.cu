@@ -343,11 +343,16 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
   if (want_dots) {  // CTA-uniform
     __shared__ double mine_dots[kLazyChunk];
     chunk_block_sum(acc, m, mine_dots, red);
-    if (threadIdx.x < kLazyChunk)
-      for (int q = 0; q < dots.n; ++q) {
-        if (dots.tag) st_pair<true>(dots.p[q], threadIdx.x, mine_dots[threadIdx.x], dots.tag);
-        else stg_cg(dots.p[q] + threadIdx.x, mine_dots[threadIdx.x]);
+    if (threadIdx.x < kLazyChunk) {
+      if (!dots.tag && dots.mc) {
+        multimem_st_f64(dots.mc + threadIdx.x, mine_dots[threadIdx.x]);
+      } else {
+        for (int q = 0; q < dots.n; ++q) {
+          if (dots.tag) st_pair<true>(dots.p[q], threadIdx.x, mine_dots[threadIdx.x], dots.tag);
+          else stg_cg(dots.p[q] + threadIdx.x, mine_dots[threadIdx.x]);
+        }
       }
+    }
   }
 }
 
@@ -472,10 +477,12 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     Dst dst;  // all-gather by peer stores
     dst.n = n.world;
     dst.tag = tg ? tag : 0ull;
+    dst.mc = (!tg && n.arena_mc) ? n.arena_mc + (act_of(l + 1, dst_buf) - A) + n.row0[l] : nullptr;
     for (int q = 0; q < n.world; ++q) dst.p[q] = act_peer(q, l + 1, dst_buf) + (size_t)n.row0[l] * (tg ? 2 : 1);
     DotOut dots;
     dots.n = n.world;
     dots.tag = tg ? tag : 0ull;
+    dots.mc = nullptr;
     dots.p[0] = nullptr;
     if (l + 1 < NL && m > 0) {
       for (int q = 0; q < n.world; ++q)
@@ -483,6 +490,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
                     (size_t)(n.rank * kLazyDotSlots + b) * kLazyChunk * (tg ? 2 : 1);
       dots.HV = A + n.off_hist_v[l + 1];
       dots.row0 = n.row0[l];
+      if (!tg && n.arena_mc) dots.mc = n.arena_mc + (dots.p[n.rank] - A);
     }
     const int kind = (snn && l == NL - 1) ? 1 : 0;
     const int segs = pick_row_segments(n.rows[l], n.ld[l], grid);

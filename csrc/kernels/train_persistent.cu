@@ -81,6 +81,7 @@ __device__ __forceinline__ void train_sample_body(const KP &p, const int grid, c
     Dst dst;
     dst.n = n.world;
     dst.tag = tg ? tag : 0ull;
+    dst.mc = (!tg && n.arena_mc) ? n.arena_mc + (act_of(n.rank, l + 1, dst_buf) - A) + n.row0[l] : nullptr;
     for (int q = 0; q < n.world; ++q) dst.p[q] = act_of(q, l + 1, dst_buf) + (size_t)n.row0[l] * (tg ? 2 : 1);
     const int kind = (snn && l == NL - 1) ? 1 : 0;
     const int segs = pick_row_segments(n.rows[l], n.ld[l], grid);

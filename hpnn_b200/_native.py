@@ -39,7 +39,7 @@ class DevNet(C.Structure):
                 ("row0", C.c_int * MAX_LAYERS), ("rows", C.c_int * MAX_LAYERS),
                 ("W", C.c_void_p * MAX_LAYERS), ("dW", C.c_void_p * MAX_LAYERS),
                 ("rank", C.c_int), ("world", C.c_int), ("arena", C.c_void_p * MAX_WORLD),
-                ("local_sync", C.c_void_p),
+                ("arena_mc", C.c_void_p), ("local_sync", C.c_void_p),
                 ("off_act", C.c_longlong * (MAX_LAYERS + 1)), ("off_part", C.c_longlong * MAX_LAYERS),
                 ("off_target", C.c_longlong), ("off_out", C.c_longlong), ("off_flags", C.c_longlong),
                 ("arena_doubles", C.c_longlong), ("part_stride", C.c_int * MAX_LAYERS),

@@ -31,6 +31,7 @@ CORE_SOURCES = [
     "csrc/core/io.cpp",
     "csrc/cpu/engine.cpp",
     "csrc/core/device_net.cu",
+    "csrc/core/symm.cu",
     "csrc/kernels/train_persistent.cu",
     "csrc/kernels/train_resident.cu",
     "csrc/kernels/train_lazy.cu",

@@ -93,19 +93,33 @@ class HpnnNet:
             else:
                 self.dW_full.append(None)
                 net.dW[l] = None
-        # ---- symmetric arena + private sync words (raw cudaMalloc: IPC-exportable)
-        self._arena_ptr = self.lib.hpnn_dev_alloc(n_doubles * 8)
+        # ---- symmetric arena + private sync words.  Several ranks: the arena is a SymmetricBuffer
+        # (VMM allocation mapped into every process, NVLS multicast address when the fabric has one;
+        # cudaMalloc + CUDA IPC as fall-back); one rank / virtual ranks: plain device memory.
+        self._symm = None
         self._sync_ptr = self.lib.hpnn_dev_alloc(256 * 4)
-        if not self._arena_ptr or not self._sync_ptr:
+        if not self._sync_ptr:
             raise MemoryError(N.last_error())
-        self.arena = torch.as_tensor(_DevBuf(self._arena_ptr, n_doubles), device=self.device)
-        net.local_sync = self._sync_ptr
-        self._peer_ptrs: List[int] = []
         for q in range(N.MAX_WORLD):
             net.arena[q] = None
-        net.arena[self.rank] = self._arena_ptr
+        net.arena_mc = None
         if self.world > 1 and not self.virtual:
-            self._exchange_arenas()
+            from ..parallel.symm import SymmetricBuffer
+
+            self._symm = SymmetricBuffer(n_doubles, group=group, device=self.device)
+            self._arena_ptr = self._symm.ptrs[self.rank]
+            for q in range(self.world):
+                net.arena[q] = self._symm.ptrs[q]
+            net.arena_mc = self._symm.mc_ptr or None
+            self.arena = self._symm.local
+        else:
+            self._arena_ptr = self.lib.hpnn_dev_alloc(n_doubles * 8)
+            if not self._arena_ptr:
+                raise MemoryError(N.last_error())
+            self.arena = torch.as_tensor(_DevBuf(self._arena_ptr, n_doubles), device=self.device)
+            net.arena[self.rank] = self._arena_ptr
+        net.local_sync = self._sync_ptr
+        self._peer_ptrs: List[int] = []
         # ---- per-sample staging: pinned result ring + device result slots
         self._n_slots = 1024
         self._res_dev = torch.zeros(self._n_slots * C.sizeof(N.TrainResult) // 8, dtype=torch.float64,
@@ -114,37 +128,20 @@ class HpnnNet:
         self._closed = False
 
     # ------------------------------------------------------------------ set-up
-    def _exchange_arenas(self):
-        import torch.distributed as dist
-
-        handle = C.create_string_buffer(64)
-        N.check(self.lib.hpnn_ipc_export(self._arena_ptr, handle), "hpnn_ipc_export")
-        mine = (self.rank, self.device.index, bytes(handle.raw))
-        everyone = [None] * self.world
-        dist.all_gather_object(everyone, mine, group=self.group)
-        for rank, _dev, raw in everyone:
-            if rank == self.rank:
-                continue
-            p = self.lib.hpnn_ipc_open(raw)
-            if not p:
-                raise RuntimeError("hpnn_ipc_open: " + N.last_error())
-            self._peer_ptrs.append(p)
-            self.net.arena[rank] = p
-        torch.cuda.synchronize(self.device)
-        dist.barrier(group=self.group)
-
     def close(self):
         if getattr(self, "_closed", True):
             return
         self._closed = True
         torch.cuda.synchronize(self.device)
-        if self.world > 1 and not self.virtual:
-            import torch.distributed as dist
-            dist.barrier(group=self.group)
-        for p in self._peer_ptrs:
-            self.lib.hpnn_ipc_close(p)
         self.arena = None
-        self.lib.hpnn_dev_free(self._arena_ptr)
+        if self._symm is not None:
+            self._symm.close()  # (synchronises with the peers: nobody unmaps while another still runs)
+            self._symm = None
+        else:
+            if self.world > 1 and not self.virtual:
+                import torch.distributed as dist
+                dist.barrier(group=self.group)
+            self.lib.hpnn_dev_free(self._arena_ptr)
         self.lib.hpnn_dev_free(self._sync_ptr)
 
     def __del__(self):

@@ -154,6 +154,9 @@ typedef struct {
   double *dW[HPNN_MAX_LAYERS];  /* momentum, same shape, or NULL            */
   int rank, world;
   double *arena[HPNN_MAX_WORLD];
+  /* NVLS multicast address of the arenas (hpnn_symm_mc_ptr), or NULL: a multimem.st to
+   * arena_mc + off lands at arena[q] + off on EVERY rank q (all-gather in one store)     */
+  double *arena_mc;
   unsigned *local_sync;         /* 256 zeroed u32 words, private to the rank */
   /* arena layout (offsets in doubles), filled by hpnn_dev_arena_layout      */
   long long off_act[HPNN_MAX_LAYERS + 1]; /* act[0]=input, act[l+1]=out of l */
@@ -208,6 +211,33 @@ int hpnn_ipc_export(void *dev_ptr, unsigned char handle[64]);
 void *hpnn_ipc_open(const unsigned char handle[64]);
 int hpnn_ipc_close(void *p);
 int hpnn_enable_peer_access(int dev, int peer);
+
+/* Symmetric memory of one NVLink / NVSwitch domain (csrc/core/symm.cu): the same-sized allocation on
+ * every rank, each rank's copy mapped into every participant, plus -- where the fabric has NVLS -- one
+ * multicast mapping through which a single multimem.st / multimem.red reaches all copies and a
+ * multimem.ld_reduce returns their sum.  Replaces the reference's gather-to-GPU-0 + broadcast copies
+ * (src/cuda_ann.cu:610-666) and its MPI_Allgather calls (src/ann.c:925).
+ * local:  one process drives all devices.  shared: one process per device; the allocation of every rank
+ * and the multicast object travel between the processes as POSIX file descriptors (the caller moves
+ * them: SCM_RIGHTS over a unix socket, hpnn_b200/parallel/symm.py).  Order for the multicast object:
+ * rank 0 mc_create -> others mc_import -> all mc_add_device -> barrier -> all mc_bind; any failure:
+ * every rank calls mc_drop and the peer mappings are used alone.  NULL / -1 on failure
+ * (hpnn_last_error()); callers then fall back to cudaMalloc + CUDA IPC. */
+typedef struct hpnn_symm hpnn_symm;
+int hpnn_symm_multicast_supported(int dev);
+hpnn_symm *hpnn_symm_create_local(const int *devs, int n, size_t bytes, int want_multicast);
+hpnn_symm *hpnn_symm_create_shared(int dev, int rank, int world, size_t bytes, int want_multicast);
+int hpnn_symm_export_fd(hpnn_symm *s);
+int hpnn_symm_import_peer(hpnn_symm *s, int peer, int fd);
+int hpnn_symm_mc_create(hpnn_symm *s);
+int hpnn_symm_mc_import(hpnn_symm *s, int fd);
+int hpnn_symm_mc_add_device(hpnn_symm *s);
+int hpnn_symm_mc_bind(hpnn_symm *s);
+void hpnn_symm_mc_drop(hpnn_symm *s);
+void *hpnn_symm_ptr(const hpnn_symm *s, int rank); /* rank's copy as mapped here (zero-filled)        */
+void *hpnn_symm_mc_ptr(const hpnn_symm *s);        /* multicast address of the set, or NULL           */
+size_t hpnn_symm_size(const hpnn_symm *s);
+void hpnn_symm_destroy(hpnn_symm *s);
 const char *hpnn_last_error(void);
 
 /* persistent per-sample kernel (K-P).  Input must already be in act[0] and the

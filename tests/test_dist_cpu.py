@@ -83,3 +83,50 @@ def test_split_rows_is_a_partition():
             assert parts[0][0] == 0 and sum(nr for _, nr in parts) == n
             assert all(parts[g][0] + parts[g][1] == parts[g + 1][0] for g in range(world - 1))
             assert max(nr for _, nr in parts) - min(nr for _, nr in parts) <= 1
+
+
+def _fd_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from hpnn_b200.parallel.symm import _all_ok, _pass_fds
+
+    import tempfile
+
+    # every rank owns an (unlinked) file; its descriptor travels to every peer
+    f = tempfile.TemporaryFile()
+    f.write(b"from%d" % rank)
+    f.flush()
+    got = _pass_fds(f.fileno(), list(range(world)), rank, world, None)
+    seen = {src: os.pread(fd, 16, 0).decode() for src, fd in got.items()}
+    # one-to-all variant (how the multicast object of rank 0 is shared)
+    f2 = tempfile.TemporaryFile()
+    f2.write(b"mc")
+    f2.flush()
+    got2 = _pass_fds(f2.fileno() if rank == 0 else None, [0], rank, world, None)
+    seen2 = {src: os.pread(fd, 16, 0).decode() for src, fd in got2.items()}
+    ok = _all_ok(rank != 1, None)
+    q.put((rank, seen, seen2, ok))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_file_descriptors_cross_processes():
+    """The plumbing of the VMM symmetric memory (hpnn_b200/parallel/symm.py): POSIX file descriptors
+    are handed from every rank to every other rank (allocation handles) and from rank 0 to all
+    (multicast object) over unix sockets."""
+    world = 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fd_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, seen, seen2, ok in res:
+        assert seen == {s: "from%d" % s for s in range(world) if s != rank}
+        assert seen2 == ({} if rank == 0 else {0: "mc"})
+        assert ok is False  # rank 1 reported a failure: everybody must see it
