@@ -202,6 +202,62 @@ __device__ __forceinline__ void panel_cols_flush(double *W, int ld, Panel pn, co
   }
 }
 
+// Momentum (BPM) top-down pass over the own panel, immediate update (src/ann.c:1996-1999,
+// cublasDger + Daxpy + Dscal in src/cuda_ann.cu:3147-3166):
+//   P[c] from the OLD weights, then  mom += (lr*d_i) h[c];  w += mom;  mom *= alpha.
+// Same organisation as the flush pass above: every thread owns column pairs, the panel's rows are
+// streamed once with two batches of four rows in flight, no cross-thread reduction.
+template <bool HS>
+__device__ __forceinline__ void panel_cols_bpm(double *W, double *M, int ld, Panel pn, const double *dsl,
+                                               const double *h, double lr, double alpha, double *Pout) {
+  const double2 zero2 = make_double2(0.0, 0.0);
+  for (int c = 2 * threadIdx.x; c < ld; c += kPanelCols) {
+    const double h0 = HS ? h[c] : ldg_cg(h + c);
+    const double h1 = HS ? h[c + 1] : ldg_cg(h + c + 1);
+    double a0 = 0.0, a1 = 0.0;
+    double2 *Wp = reinterpret_cast<double2 *>(W + (size_t)pn.r0 * ld + c);
+    double2 *Mp = reinterpret_cast<double2 *>(M + (size_t)pn.r0 * ld + c);
+    const size_t stride2 = (size_t)(ld >> 1);
+    double2 wa[4], ma[4], wb[4], mb[4];
+    auto load = [&](double2 (&w)[4], double2 (&m)[4], int i0) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const bool on = i0 + u < pn.cnt;
+        w[u] = on ? ldw2<true>(Wp + (size_t)(i0 + u) * stride2) : zero2;
+        m[u] = on ? ldw2<true>(Mp + (size_t)(i0 + u) * stride2) : zero2;
+      }
+    };
+    auto consume = [&](double2 (&w)[4], double2 (&m)[4], int i0) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u;
+        if (i < pn.cnt) {
+          const double d = dsl[i];
+          a0 = fma(w[u].x, d, a0);
+          a1 = fma(w[u].y, d, a1);
+          const double s = lr * d;
+          m[u].x = fma(s, h0, m[u].x);
+          m[u].y = fma(s, h1, m[u].y);
+          w[u].x += m[u].x;
+          w[u].y += m[u].y;
+          stw2<true>(Wp + (size_t)i * stride2, w[u]);
+          m[u].x *= alpha;
+          m[u].y *= alpha;
+          stw2<true>(Mp + (size_t)i * stride2, m[u]);
+        }
+      }
+    };
+    load(wa, ma, 0);
+    for (int i0 = 0; i0 < pn.cnt; i0 += 8) {
+      load(wb, mb, i0 + 4);
+      consume(wa, ma, i0);
+      load(wa, ma, i0 + 8);
+      consume(wb, mb, i0 + 4);
+    }
+    stg_cg2(reinterpret_cast<double2 *>(Pout + c), make_double2(a0, a1));
+  }
+}
+
 // sums of 8 values over the 32 lanes with 9 exchanges instead of 40: every step halves the number
 // of values a lane is responsible for.  Returns the complete sum of value ((lane >> 2) & 7).
 __device__ __forceinline__ double reduce8(const double (&pr)[8], int lane) {
@@ -409,6 +465,9 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   const bool snn = p.type == HPNN_TYPE_SNN;
   const int depth = p.lazy_depth;
   const bool multi = n.world > 1;
+  // momentum: immediate updates (depth 1, no pending factors), the momentum rows of a panel are
+  // only ever touched by the CTA that owns the panel
+  const bool bpm = p.train == HPNN_TRAIN_BPM;
   constexpr bool tg = TG;
   const unsigned long long launch = (unsigned long long)ld_relaxed_gpu(n.local_sync + 160) + 1ull;
   auto tag_of = [&](int iteration) { return (launch << 32) | (unsigned long long)(unsigned)iteration; };
@@ -464,8 +523,21 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     }
     s = block_sum(s, red);
     if (threadIdx.x < kLazyChunk) coef0[threadIdx.x] = threadIdx.x == 0 ? s : 0.0;
-    for (int i = threadIdx.x; i < pmax; i += kThreads) us[(size_t)i * kLazyChunk] = 0.0;
+    for (int i = threadIdx.x; i < pmax; i += kThreads) {
+      us[(size_t)i * kLazyChunk] = 0.0;      // ubar
+      us[(size_t)i * kLazyChunk + 1] = 0.0;  // BPM: mu, the momentum of layer 0 in factored form (M0 = mu (x) x)
+    }
     __syncthreads();
+  }
+  if (bpm) {
+    // the momentum is zeroed per sample (src/ann.c:2386); own panel rows only, so no barrier is needed
+    // before the owning CTA reads them in its first top-down pass
+    for (int l = 1; l < NL; ++l) {
+      const Panel pn = panel_of(n.rows[l], grid, b);
+      double2 *m2 = reinterpret_cast<double2 *>(n.dW[l] + (size_t)pn.r0 * n.ld[l]);
+      const size_t tot = (size_t)pn.cnt * n.ld[l] / 2;
+      for (size_t i = threadIdx.x; i < tot; i += kThreads) stw2<true>(m2 + i, make_double2(0.0, 0.0));
+    }
   }
   auto forward = [&](int l, int src_buf, int dst_buf, int m, unsigned long long tag) {
     stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
@@ -559,7 +631,8 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
           stg_cg(HV + (size_t)c * kLazyChunk + m, tg ? h[c] : ldg_cg(h + c));
         if (pn.cnt > 0) panel_cols_read(n.W[l], n.ld[l], pn, dsl, Pout);
       } else if (pn.cnt > 0) {
-        panel_cols_flush<TG>(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
+        if (bpm) panel_cols_bpm<TG>(n.W[l], n.dW[l], n.ld[l], pn, dsl, h, p.lr, p.alpha, Pout);
+        else panel_cols_flush<TG>(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
       }
       trace(100 + l);
       prefetch_panel(l - 1);  // streamed next: top-down of layer l-1, or the forward pass of layer 0
@@ -649,7 +722,16 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     // ---- bottom-up: layer 0 update fused with its forward, then the read-only layers
     {
       const Panel p0 = panel(0);
-      for (int i = threadIdx.x; i < p0.cnt; i += kThreads) us[(size_t)i * kLazyChunk] += p.lr * dsl[i];  // ubar
+      if (!bpm) {
+        for (int i = threadIdx.x; i < p0.cnt; i += kThreads) us[(size_t)i * kLazyChunk] += p.lr * dsl[i];  // ubar
+      } else {
+        // dw += lr*delta (x) x; W += dw; dw *= alpha with dw = mu (x) x: the triple acts on the row scalars
+        for (int i = threadIdx.x; i < p0.cnt; i += kThreads) {
+          const double mu = us[(size_t)i * kLazyChunk + 1] + p.lr * dsl[i];
+          us[(size_t)i * kLazyChunk] += mu;
+          us[(size_t)i * kLazyChunk + 1] = mu * p.alpha;
+        }
+      }
     }
     forward(0, 0, cur ^ 1, m, tag);  // (stages x and synchronises before ubar is read)
     trace(300);
@@ -691,6 +773,11 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
         w.x = fma(ub, x2[c].x, w.x);
         w.y = fma(ub, x2[c].y, w.y);
         stg_cg2(w2 + c, w);
+      }
+      if (bpm) {  // leave the momentum matrix of layer 0 as the immediate updates would have: mu (x) x
+        const double mu = us[(size_t)i * kLazyChunk + 1];
+        double2 *m2 = reinterpret_cast<double2 *>(n.dW[0] + (size_t)(p0.r0 + i) * n.ld[0]);
+        for (int c = lane; c < (n.ld[0] >> 1); c += 32) stg_cg2(m2 + c, make_double2(mu * x2[c].x, mu * x2[c].y));
       }
     }
   }
@@ -750,11 +837,14 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
   const int disabled = g_lazy_panel >= 0 ? !g_lazy_panel : disabled_env;
   const int depth = lazy_depth_setting();
   const hpnn_dev_net &n = p_in.net;
-  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || p_in.train != HPNN_TRAIN_BP ||
+  const bool bpm = p_in.train == HPNN_TRAIN_BPM;
+  if (disabled || depth < 2 || grid > kLazyDotSlots || p_in.mode != 0 || (p_in.train != HPNN_TRAIN_BP && !bpm) ||
       n.hist_depth < 2 || n.panel_stride <= 0 || n.n_layers < 2)
     return 1;
   KP p = p_in;
-  p.lazy_depth = depth < n.hist_depth ? depth : n.hist_depth;
+  // momentum cannot be deferred cheaply (the stored momentum matrix would need a second factor series,
+  // docs/ROADMAP.md): BPM runs the same row-panel organisation with immediate updates (depth 1)
+  p.lazy_depth = bpm ? 1 : (depth < n.hist_depth ? depth : n.hist_depth);
   {
     static const long long prefetch_mb = [] {
       const char *e = getenv("HPNN_PREFETCH_MB");

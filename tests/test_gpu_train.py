@@ -167,3 +167,33 @@ def test_deferred_update_trainer_on_the_wide_bench_width():
         np.testing.assert_allclose(a, b, atol=1e-11)
     gpu.close()
     cpu.close()
+
+
+@pytest.mark.parametrize("nn_type", [N.TYPE_ANN, N.TYPE_SNN])
+def test_row_panel_momentum_trainer_matches_cpu_engine(nn_type):
+    """BPM on the row-panel trainer (K-PL1 with immediate updates): the momentum triple
+    dw += lr*delta (x) h; W += dw; dw *= alpha (src/ann.c:1996-1999) applied by the CTA that owns the
+    panel, layer 0 in factored form.  Fixed iteration counts, weights equal to the CPU engine's."""
+    lib = N.load()
+    lib.hpnn_dev_set_lazy(8, 0)  # reserve the panel slots for every shape
+    lib.hpnn_dev_set_lazy_panel(1)
+    try:
+        for n_in, hid, n_out in [(40, (600, 300, 150), 12), (24, (4200, 310), 10)]:
+            k, _ = hp.generate_kernel(77, n_in, list(hid), n_out)
+            X, T = make_problem(nn_type, n_in, hid, n_out, n_samples=2, seed=3)
+            for n_it in (1, 9, 22):
+                kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
+                gpu = CudaEngine(k, nn_type, N.TRAIN_BPM, **kw)
+                assert gpu.net.net.panel_stride > 0
+                cpu = CpuEngine(k, nn_type, N.TRAIN_BPM, cuda_defaults=True, **kw)
+                for x, t in zip(X, T):
+                    rg, rc = gpu.train(x, t), cpu.train(x, t)
+                    assert rg.n_iter == rc.n_iter == n_it
+                    assert abs(rg.init_err - rc.init_err) < 1e-12 and abs(rg.last_err - rc.last_err) < 1e-11
+                for a, b in zip(gpu.kernel().weights, cpu.kernel().weights):
+                    np.testing.assert_allclose(a, b, atol=1e-11)
+                gpu.close()
+                cpu.close()
+    finally:
+        lib.hpnn_dev_set_lazy(-1, -1)
+        lib.hpnn_dev_set_lazy_panel(-1)

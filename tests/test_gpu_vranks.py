@@ -38,9 +38,10 @@ def test_streaming_trainer_on_virtual_ranks(monkeypatch, world, proto, nn_type, 
     cpu.close()
 
 
+@pytest.mark.parametrize("train", [N.TRAIN_BP, N.TRAIN_BPM])
 @pytest.mark.parametrize("proto", ["barrier", "tagged"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto):
+def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto, train):
     """K-PL1 with several ranks: per-rank column-slice sums scattered to the owning rank, forward
     results and partial dot products stored into every rank's arena; 19 iterations = two
     write-back periods of 8 plus a partial one."""
@@ -55,9 +56,9 @@ def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto):
             X, T = make_problem(nn_type, n_in, hid, n_out, n_samples=2, seed=3)
             n_it = 19
             kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
-            eng = make_engine(f"virtual:{world}", k, nn_type, N.TRAIN_BP, **kw)
+            eng = make_engine(f"virtual:{world}", k, nn_type, train, **kw)
             assert eng.nets[0].net.hist_depth == 8 and eng.nets[0].net.panel_stride > 0
-            cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw)
+            cpu = CpuEngine(k, nn_type, train, cuda_defaults=True, **kw)
             for x, t in zip(X, T):
                 a, b = eng.train(x, t), cpu.train(x, t)
                 assert a.n_iter == b.n_iter == n_it
