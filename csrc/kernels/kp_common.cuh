@@ -120,10 +120,10 @@ __device__ __forceinline__ unsigned long long watch_peek() {
 // at k+1 (ordered after the reset).  The barrier index survives kernel launches in
 // local_sync, so the rotation simply continues with the next sample.
 //
-// With several ranks CTA 0 alone watches the counter, exchanges one flag word with every
-// peer over NVLink (fence.sys + relaxed stores, relaxed polling + fence.sys) and then
-// publishes the index in a `go` word the other CTAs poll.
-// local_sync words: [0],[32],[64] counters (own 128 B lines), [96] go, [128] saved index.
+// With several ranks CTA 0 alone watches the counter and publishes one flag word per rank over
+// NVLink (fence.sys + relaxed stores, or one multimem.st); every CTA polls the flag words of all
+// ranks in its own arena and issues one fence.sys.
+// local_sync words: [0],[32],[64] counters (own 128 B lines), [128] saved index, [160] launch id.
 struct Barrier {
   unsigned *sync;
   unsigned k;     // barrier index, meaningful in thread 0
@@ -172,36 +172,32 @@ struct Barrier {
         }
         if (bid == 0) *prev = 0;
         fence_gpu();
-      } else if (bid == 0) {
-        while (ld_relaxed_gpu(c) != grid) {
-          if (sp.give_up()) break;
-        }
-        *prev = 0;
+      } else {
+        // Several ranks.  CTA 0 alone watches the local counter and then publishes this rank's flag word
+        // (= barrier index) on EVERY rank, itself included: one multimem.st when the arenas have a
+        // multicast mapping, a store per rank otherwise.  Every CTA -- not only CTA 0 -- then polls the
+        // `world` flag words of its own arena directly (one 64-byte line): no relay through a "go" word.
         const unsigned long long we = (unsigned long long)k;
-        fence_sys();  // release: everything this rank wrote is visible before the flags
-        if (n.arena_mc) {  // one multicast store sets this rank's flag word on every rank
-          multimem_st_u64(reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags) + n.rank, we);
-        } else {
-          for (int q = 0; q < n.world; ++q) {
-            if (q == n.rank) continue;
-            unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank;
-            st_relaxed_sys(f, we);
+        if (bid == 0) {
+          while (ld_relaxed_gpu(c) != grid) {
+            if (sp.give_up()) break;
+          }
+          *prev = 0;
+          fence_sys();  // release: everything this rank wrote is visible before the flags
+          if (n.arena_mc) {
+            multimem_st_u64(reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags) + n.rank, we);
+          } else {
+            for (int q = 0; q < n.world; ++q)
+              st_relaxed_sys(reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank, we);
           }
         }
         const unsigned long long *mine = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
         for (int q = 0; q < n.world; ++q) {
-          if (q == n.rank) continue;
           while (ld_relaxed_sys(mine + q) < we) {
             if (sp.give_up()) break;
           }
         }
-        fence_sys();  // acquire: the peers' stores into this arena are visible after it
-        st_release_gpu(sync + 96, k);
-      } else {
-        while (ld_relaxed_gpu(sync + 96) != k) {
-          if (sp.give_up()) break;
-        }
-        fence_gpu();
+        fence_sys();  // acquire: the peers' (and the other local CTAs') stores are visible after it
       }
     }
     __syncthreads();

@@ -542,10 +542,12 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   auto forward = [&](int l, int src_buf, int dst_buf, int m, unsigned long long tag) {
     stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
     __syncthreads();
+    trace(600 + l);  // input vector staged (tagged mode: every producer's value has arrived)
     if (l >= 1 && m > 0) {  // coef[j] = v_j . x
       if (tg) gather_dots_tagged(n, l, m, tag, coef, red, grid);
       else gather_dots(n, l, m, coef, red, grid);
     }
+    trace(700 + l);  // partial dot products gathered
     Dst dst;  // all-gather by peer stores
     dst.n = n.world;
     dst.tag = tg ? tag : 0ull;
@@ -690,6 +692,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
         }
       }
       if (multi) {
+        trace(800 + l);  // column-slice sums formed and sent to their owners
         if (!tg) bar.sync_all(n, slice.cnt > 0);
         trace(500 + l);
         const Panel below = panel(l - 1);

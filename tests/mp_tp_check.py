@@ -43,6 +43,9 @@ def main():
         X, T = problem(nn_type, n_in, n_out, 3, 11)
         kw = dict(max_iter=400)
         fused = CudaEngine(k, nn_type, train, group=group, **kw)
+        if rank == 0 and n_in == 64:
+            sy = fused.net._symm
+            print(f"case symmetric-memory backend={sy.backend} multicast={'yes' if sy.mc_ptr else 'no'} world={world}", flush=True)
         coll = CollectiveTPEngine(k, nn_type, train, group=group, device=f"cuda:{torch.cuda.current_device()}", **kw)
         cpu = CpuEngine(k, nn_type, train, cuda_defaults=True, **kw) if rank == 0 else None
         t_f = t_c = 0.0
