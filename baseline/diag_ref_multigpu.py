@@ -84,7 +84,7 @@ def main():
                            CUDA_LAUNCH_BLOCKING=blocking, OMP_NUM_THREADS="2")
                 try:
                     r = subprocess.run([str(exe), "-v", "-v", "-v", "-S", str(streams), "nn.conf"], cwd=d, env=env,
-                                       capture_output=True, text=True, timeout=180)
+                                       capture_output=True, text=True, timeout=40)
                     rc, so, se = r.returncode, r.stdout, r.stderr
                 except subprocess.TimeoutExpired:
                     rc, so, se = -999, "", "timeout"
