@@ -70,19 +70,24 @@ def main():
                 ms = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
                 if world > 1:
                     dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
+                tr = buf.cpu().numpy().reshape(-1, 2)
+                tr = tr[tr[:, 0] != 0]
+                starts = np.where(tr[:, 0] == 1)[0]
+                seg = defaultdict(list)
+                for s0, s1 in zip(starts[3:-1], starts[4:]):
+                    for j in range(s0 + 1, s1 + 1):
+                        seg[(int(tr[j - 1, 0]), int(tr[j, 0]))].append(int(tr[j, 1] - tr[j - 1, 1]))
+                phases = {f"{a_}->{b_}": round(float(np.mean(v))) for (a_, b_), v in seg.items()}
+                by_rank = [phases]
+                if world > 1:  # CTA 0 of EVERY rank: who waits for whom
+                    by_rank = [None] * world
+                    dist.all_gather_object(by_rank, phases, group=group)
                 if rank == 0:
                     us = float(ms.item()) * 1e3 / r.n_iter
-                    tr = buf.cpu().numpy().reshape(-1, 2)
-                    tr = tr[tr[:, 0] != 0]
-                    starts = np.where(tr[:, 0] == 1)[0]
-                    seg = defaultdict(list)
-                    for s0, s1 in zip(starts[3:-1], starts[4:]):
-                        for j in range(s0 + 1, s1 + 1):
-                            seg[(int(tr[j - 1, 0]), int(tr[j, 0]))].append(int(tr[j, 1] - tr[j - 1, 1]))
-                    phases = {f"{a_}->{b_}": round(float(np.mean(v))) for (a_, b_), v in seg.items()}
                     print(json.dumps({"config": name, "world": world, "protocol": proto, "iterations": r.n_iter,
                                       "us_per_iteration": round(us, 2), "iterations_per_s": round(1e6 / us, 1),
-                                      "last_err": r.last_err, "phase_cycles": phases}), flush=True)
+                                      "last_err": r.last_err, "phase_cycles": phases,
+                                      "phase_cycles_by_rank": by_rank}), flush=True)
             eng.close()
         dist.barrier()
     dist.destroy_process_group()

@@ -395,16 +395,15 @@ static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
   p.max_iter = o->max_iter >= 0 ? o->max_iter : d.max_iter;
   p.result = result_dev;
   {
-    // The tagged hand-over costs one NVLink flight per phase; the fence + flag barrier costs a
-    // system-scope fence (a round trip while peer stores are in flight) plus the flag flight and
-    // a relay through CTA 0, ~10 us on 8 GPUs.  Tagged therefore wins whenever a phase is short:
-    // always for nets that stream < 48 MB per rank, and for ANY net from 4 ranks on (a rank's
-    // share of an 8192 x 8192 layer streams in ~10 us at 8 ranks).  Polling every vector costs
-    // ~2% when the phases are long (2 ranks, 8192-wide layers), so those keep the barrier.
+    // Tagged hand-over for nets that stream < 48 MB per rank: their phases last a few microseconds and
+    // a {value, tag} pair needs no fence at all (2x on SNN 784-1000-1000-10 at 4 GPUs).  Wide layers keep
+    // plain buffers + the flag barrier: measured on 784-8192x4-10 the tagged variant pays ~10 k cycles
+    // per phase for polling and unpacking 8192 pairs in every CTA (457 vs 405 us/iteration at 2 ranks,
+    // profiles/r2_probe2b_wide.jsonl), and since the barrier got down to one fence.sys it costs ~9 k.
     const char *proto = getenv("HPNN_TP_PROTOCOL");
     long long local_doubles = 0;
     for (int l = 0; l < net->n_layers; ++l) local_doubles += (long long)net->rows[l] * net->ld[l];
-    bool tagged = net->world > 1 && (local_doubles * 8 < (48LL << 20) || net->world >= 4);
+    bool tagged = net->world > 1 && local_doubles * 8 < (48LL << 20);
     if (proto && !strcmp(proto, "barrier")) tagged = false;
     if (proto && !strcmp(proto, "tagged")) tagged = net->world > 1;
     p.tagged = tagged ? 1 : 0;
