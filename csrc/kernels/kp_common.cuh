@@ -9,6 +9,7 @@ namespace hpnn {
 constexpr int kMaxRsplit = 4;  // row parts of a column task (see phase_cols)
 constexpr int kLazyChunk = 8;  // update factors kept per row / column by the deferred-update trainer
 constexpr int kLazyDotSlots = 160;  // per-CTA partial dot product slots per rank (>= grid size)
+constexpr int kFoldMaxOut = 32;  // widest output layer the row-panel trainer folds into the layer below it
 constexpr size_t kMaxDynSmem = 226 * 1024;  // dynamic shared memory per CTA (227 KB minus the static variables)
 constexpr long long kLazyMinBytes = 64LL << 20;  // local weights of layers >= 1 below this: not worth it
 
@@ -24,6 +25,7 @@ struct KP {
   hpnn_train_result *result;
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
+  int fold_out;  // K-PL1: the output layer is folded into the phases of the layer below (see train_lazy1.cu)
   int fault;  // fault injection (tests): 1 = this rank leaves at kernel entry, as if its launch had failed
   unsigned long long spin_budget_ns;  // longest time any wait may take before the job is abandoned (0 = unbounded)
 };

@@ -359,7 +359,8 @@ __device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, cons
 template <int UPD>
 __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
                                            int act_kind, const Dst &dst, int segs, double *zpart, const double *us,
-                                           const double *coef, int mcorr, int m, const DotOut &dots, double *red) {
+                                           const double *coef, int mcorr, int m, const DotOut &dots, double *red,
+                                           double *ykeep = nullptr) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int nz;  // partials per row
   if (ld >= 4 * kPanelCols) {
@@ -394,6 +395,7 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
     }
     const double y = act_kind == 0 ? act_f(z) : z;
     dst_store(dst, pn.r0 + i, y);
+    if (ykeep) ykeep[i] = y;  // own outputs stay in shared memory (folded output layer)
     if (want_dots) chunk_fma(dots.HV + (size_t)(dots.row0 + pn.r0 + i) * kLazyChunk, y, m, acc);
   }
   if (want_dots) {  // CTA-uniform
@@ -458,6 +460,9 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   double *us = dsl + pmax;           // u factors of the own panels: [layer][row][8]
   double *red = us + (size_t)NL * pmax * kLazyChunk;
   double *rowpart = red + kRedDoubles;
+  double *ylast = rowpart + (size_t)pmax * kZStride;  // own outputs of the last hidden layer (folded output layer)
+  double *zs = ylast + pmax;                          // output vector / output deltas, kFoldMaxOut each
+  double *dlast = zs + kFoldMaxOut;
   __shared__ double coef[kLazyChunk];
 
   const int n_out = n.dims[NL];
@@ -469,6 +474,22 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   // only ever touched by the CTA that owns the panel
   const bool bpm = p.train == HPNN_TRAIN_BPM;
   constexpr bool tg = TG;
+  // Output layer folded into the layer below it (narrow output layers, plain-buffer protocol).  A
+  // 10 x 8192 output layer is 0.04% of the weights but used to cost four phases and four barriers
+  // per iteration.  Instead every rank keeps a working copy WL of the whole layer in its arena and
+  // uses only the COLUMNS that match its own rows of the last hidden layer:
+  //   forward : the CTA that has just produced outputs y of its panel adds WL[:, panel] . y and
+  //             publishes <= 32 partial sums per CTA; after the phase barrier of the hidden layer
+  //             every CTA adds the partial sums of all CTAs and ranks in a fixed order;
+  //   backward: delta_out is known to every CTA (redundant evaluation), so the CTA forms
+  //             WL[:, panel]^T delta_out, the hidden deltas of its panel and the BP / BPM update of
+  //             those columns locally: no phase, no barrier;
+  //   sample end: the column slices are gathered into every rank's copy and the owners of the rows
+  //             copy them back to the weight storage.
+  const bool fold = !TG && p.fold_out != 0;
+  const int NLw = fold ? NL - 1 : NL;  // layers that have phases of their own
+  double *WL = A + n.off_wlast, *ML = A + n.off_mlast;
+  const int ldl = n.ld[NL - 1];
   const unsigned long long launch = (unsigned long long)ld_relaxed_gpu(n.local_sync + 160) + 1ull;
   auto tag_of = [&](int iteration) { return (launch << 32) | (unsigned long long)(unsigned)iteration; };
 
@@ -532,13 +553,51 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   if (bpm) {
     // the momentum is zeroed per sample (src/ann.c:2386); own panel rows only, so no barrier is needed
     // before the owning CTA reads them in its first top-down pass
-    for (int l = 1; l < NL; ++l) {
+    for (int l = 1; l < NLw; ++l) {
       const Panel pn = panel_of(n.rows[l], grid, b);
       double2 *m2 = reinterpret_cast<double2 *>(n.dW[l] + (size_t)pn.r0 * n.ld[l]);
       const size_t tot = (size_t)pn.cnt * n.ld[l] / 2;
       for (size_t i = threadIdx.x; i < tot; i += kThreads) stw2<true>(m2 + i, make_double2(0.0, 0.0));
     }
   }
+  if (fold) {
+    // working copy of the output layer: every rank contributes its rows to every rank's copy (first
+    // used after the barrier of the first forward phase); momentum copy starts from zero
+    const int lr_ = NL - 1;
+    const size_t tot = (size_t)n.rows[lr_] * ldl;
+    for (size_t i = (size_t)b * kThreads + threadIdx.x; i < tot; i += (size_t)grid * kThreads) {
+      const double v = ldg_cg(n.W[lr_] + i);
+      const size_t off = (size_t)n.off_wlast + (size_t)n.row0[lr_] * ldl + i;
+      if (n.arena_mc) multimem_st_f64(n.arena_mc + off, v);
+      else
+        for (int q = 0; q < n.world; ++q) stg_cg(n.arena[q] + off, v);
+    }
+    if (bpm) {
+      const size_t all = (size_t)n_out * ldl;
+      for (size_t i = (size_t)b * kThreads + threadIdx.x; i < all; i += (size_t)grid * kThreads) stg_cg(ML + i, 0.0);
+    }
+  }
+  // folded output layer, forward part: this CTA's share of WL . y, one slot per (rank, CTA) on every rank
+  auto fold_publish = [&]() {
+    const Panel pn = panel_of(n.rows[NL - 2], grid, b);
+    const int col0 = n.row0[NL - 2] + pn.r0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();  // ylast complete
+    for (int r = warp; r < n_out; r += kWarps) {
+      double s = 0.0;
+      for (int i = lane; i < pn.cnt; i += 32) s = fma(ldg_cg(WL + (size_t)r * ldl + col0 + i), ylast[i], s);
+#pragma unroll
+      for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) zs[r] = s;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < n_out && pn.cnt > 0) {
+      const size_t off = (size_t)n.off_zpart + ((size_t)(n.rank * kLazyDotSlots + b) * kFoldMaxOut + threadIdx.x);
+      if (n.arena_mc) multimem_st_f64(n.arena_mc + off, zs[threadIdx.x]);
+      else
+        for (int q = 0; q < n.world; ++q) stg_cg(n.arena[q] + off, zs[threadIdx.x]);
+    }
+  };
   auto forward = [&](int l, int src_buf, int dst_buf, int m, unsigned long long tag) {
     stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
     __syncthreads();
@@ -558,7 +617,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     dots.tag = tg ? tag : 0ull;
     dots.mc = nullptr;
     dots.p[0] = nullptr;
-    if (l + 1 < NL && m > 0) {
+    if (l + 1 < NLw && m > 0) {
       for (int q = 0; q < n.world; ++q)
         dots.p[q] = n.arena[q] + n.off_hist_dot[l + 1] +
                     (size_t)(n.rank * kLazyDotSlots + b) * kLazyChunk * (tg ? 2 : 1);
@@ -568,18 +627,45 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     }
     const int kind = (snn && l == NL - 1) ? 1 : 0;
     const int segs = pick_row_segments(n.rows[l], n.ld[l], grid);
+    const bool feeds_out = fold && l == NL - 2;
     panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, dst, segs, rowpart, us_of(l),
-                  l == 0 ? coef0 : coef, l == 0 ? 1 : m, m, dots, red);
+                  l == 0 ? coef0 : coef, l == 0 ? 1 : m, m, dots, red, feeds_out ? ylast : nullptr);
+    if (feeds_out) fold_publish();
   };
 
-  for (int l = 0; l < NL; ++l) {
+  for (int l = 0; l < NLw; ++l) {
     forward(l, cur, cur, 0, tag_of(0));
     phase_sync(panel(l).cnt > 0);
   }
   const double *target = A + n.off_target;
-  const int last = NL - 1;
-  const Panel plast = panel(last);
-  const int out_row0 = n.row0[last] + plast.r0;
+  const int last = NLw - 1;  // top-most layer with phases of its own
+  const Panel plast = panel(NL - 1);
+  const int out_row0 = n.row0[NL - 1] + plast.r0;
+  // folded output layer: the output vector from the per-CTA partial sums of all ranks (rank-major, CTA
+  // order: the same order on every CTA and every rank), then the usual statistics; dlast = all output deltas
+  auto evaluate_fold = [&](double *o_out) -> OutStats {
+    const double *zp = A + n.off_zpart;
+    const int lanes = n_out <= 16 ? 16 : 32, nparts = kThreads / lanes;
+    const int r = threadIdx.x % lanes, part = threadIdx.x / lanes;
+    const int nprev = n.dims[NL - 1];
+    double s = 0.0;
+    __syncthreads();
+#pragma unroll 4
+    for (int idx = part; idx < n.world * kLazyDotSlots; idx += nparts) {
+      const int q = idx / kLazyDotSlots, bb = idx % kLazyDotSlots;
+      const int rows_q = row0_of(q + 1, nprev, n.world) - row0_of(q, nprev, n.world);
+      if (bb < grid && bb < rows_q && r < n_out) s += ldg_cg(zp + (size_t)idx * kFoldMaxOut + r);
+    }
+    red[part * lanes + r] = s;
+    __syncthreads();
+    if ((int)threadIdx.x < n_out) {
+      double z = 0.0;
+      for (int q = 0; q < nparts; ++q) z += red[q * lanes + threadIdx.x];
+      zs[threadIdx.x] = snn ? z : act_f(z);
+    }
+    __syncthreads();
+    return output_stats<true>(p.type, p.stable, zs, target, n_out, 0, n_out, dlast, o_out, red);
+  };
   // output statistics from the gathered output vector (tagged mode: gathered into xs first)
   auto evaluate = [&](unsigned long long tag, int row0, int rows, double *dsp, double *o_out) -> OutStats {
     if (tg) {
@@ -590,7 +676,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     }
     return output_stats(p.type, p.stable, act_of(NL, cur), target, n_out, row0, rows, dsp, o_out, red);
   };
-  OutStats st = evaluate(tag_of(0), out_row0, plast.cnt, dsl, nullptr);
+  OutStats st = fold ? evaluate_fold(nullptr) : evaluate(tag_of(0), out_row0, plast.cnt, dsl, nullptr);
   double E = st.err;
   const double init_err = E;
   int iter = 0, ok = (st.argmax == st.target), first_ok = 0;
@@ -603,6 +689,33 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     const unsigned long long abort_seen = watch_peek();
     const unsigned long long tag = tag_of(iter);
     const bool flush = (m + 1 >= depth);
+    if (fold) {
+      // output layer, backward part: hidden deltas of the own panel from the OLD columns, then the
+      // BP / BPM update of exactly those columns (src/ann.c:1644, 1996-1999), all inside this CTA
+      const Panel pn = panel(NL - 2);
+      const int col0 = n.row0[NL - 2] + pn.r0;
+      for (int i = threadIdx.x; i < pn.cnt; i += kThreads) {
+        const double h = ylast[i];
+        double P = 0.0;
+        for (int r = 0; r < n_out; ++r) {
+          double *wp = WL + (size_t)r * ldl + col0 + i;
+          double w = ldg_cg(wp);
+          const double d = dlast[r];
+          P = fma(w, d, P);
+          if (!bpm) {
+            w = fma(p.lr * d, h, w);
+          } else {
+            double *mp = ML + (size_t)r * ldl + col0 + i;
+            const double mm = fma(p.lr * d, h, ldg_cg(mp));
+            w += mm;
+            stg_cg(mp, mm * p.alpha);
+          }
+          stg_cg(wp, w);
+        }
+        dsl[i] = P * dact_f(h);
+      }
+      __syncthreads();
+    }
     // ---- top-down
     for (int l = last; l >= 1; --l) {
       const Panel pn = panel(l);
@@ -741,16 +854,16 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     prefetch_panel(1);
     phase_sync(panel(0).cnt > 0);
     trace(400);
-    for (int l = 1; l < NL; ++l) {
+    for (int l = 1; l < NLw; ++l) {
       forward(l, cur ^ 1, cur ^ 1, m, tag);
       trace(300 + l);
-      prefetch_panel(l + 1 < NL ? l + 1 : last - 1);  // after the last layer: the first wide top-down pass
+      prefetch_panel(l + 1 < NLw ? l + 1 : last - 1);  // after the last layer: the first wide top-down pass
       phase_sync(panel(l).cnt > 0);
       trace(400 + l);
     }
     cur ^= 1;
     watch_publish(abort_seen);
-    st = evaluate(tag, out_row0, plast.cnt, dsl, nullptr);
+    st = fold ? evaluate_fold(nullptr) : evaluate(tag, out_row0, plast.cnt, dsl, nullptr);
     trace(2);
     if (s_watch.exit_now) break;  // the job was abandoned (a wait ran out of time)
     dE = E - st.err;
@@ -788,13 +901,37 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     __syncthreads();
     for (int i = threadIdx.x; i < pmax; i += kThreads) dsl[i] = 0.0;  // lr == 0 and no sums are wanted
     __syncthreads();
-    for (int l = 1; l < NL; ++l) {
+    for (int l = 1; l < NLw; ++l) {
       const Panel pn = panel(l);
       if (pn.cnt > 0)
         panel_cols_flush<false>(n.W[l], n.ld[l], pn, dsl, us_of(l), A + n.off_hist_v[l], act_of(l, cur), 0.0, m, nullptr);
     }
   }
-  if (b == 0) evaluate(tag_of(iter), 0, 0, nullptr, A + n.off_out);  // publish the final (normalised) output
+  if (fold) {
+    if (b == 0) evaluate_fold(A + n.off_out);  // publish the final (normalised) output
+    // the updated column slice of the output layer into every rank's working copy ...
+    const Panel pn = panel(NL - 2);
+    const int col0 = n.row0[NL - 2] + pn.r0;
+    if (n.world > 1) {
+      for (int idx = threadIdx.x; idx < n_out * pn.cnt; idx += kThreads) {
+        const size_t off = (size_t)n.off_wlast + (size_t)(idx / pn.cnt) * ldl + col0 + idx % pn.cnt;
+        const double v = ldg_cg(A + off);
+        if (n.arena_mc) multimem_st_f64(n.arena_mc + off, v);
+        else
+          for (int q = 0; q < n.world; ++q)
+            if (q != n.rank) stg_cg(n.arena[q] + off, v);
+      }
+    }
+    bar.sync_all(n, true);
+    // ... and the rows this rank owns back to the weight storage
+    const int lr_ = NL - 1;
+    const size_t tot = (size_t)n.rows[lr_] * ldl;
+    const double *src = WL + (size_t)n.row0[lr_] * ldl;
+    for (size_t i = (size_t)b * kThreads + threadIdx.x; i < tot; i += (size_t)grid * kThreads)
+      stg_cg(n.W[lr_] + i, ldg_cg(src + i));
+  } else if (b == 0) {
+    evaluate(tag_of(iter), 0, 0, nullptr, A + n.off_out);  // publish the final (normalised) output
+  }
   bar.finish();
   if (b == 0 && threadIdx.x == 0) n.local_sync[160] = (unsigned)launch;
   if (b == 0 && threadIdx.x == 0 && p.result) {
@@ -864,8 +1001,16 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
   pmax = (pmax + 7) & ~7;
   rowpart = pmax * kZStride;
   p.max_rows = pmax;  // the kernel's carve-up uses the panel height, not the layer height
-  const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart);
+  const size_t smem = sizeof(double) * ((size_t)p.max_ld + pmax + (size_t)n.n_layers * pmax * kLazyChunk + kRedDoubles + rowpart +
+                                       pmax + 2 * kFoldMaxOut);
   if (smem > kMaxDynSmem) return 1;
+  {
+    static const int fold_env = [] {
+      const char *e = getenv("HPNN_FOLD_OUT");
+      return (e && !strcmp(e, "0")) ? 0 : 1;
+    }();
+    p.fold_out = (fold_env && !p.tagged && n.off_zpart > 0 && n.dims[n.n_layers] <= kFoldMaxOut && n.n_layers >= 3) ? 1 : 0;
+  }
   p_out = p;
   smem_out = smem;
   return 0;

@@ -373,6 +373,16 @@ long long hpnn_dev_arena_layout(hpnn_dev_net *net) {
     net->off_panel = off;
     off += 2LL * kLazyDotSlots * net->panel_stride;
   }
+  net->off_wlast = net->off_mlast = net->off_zpart = 0;
+  if (net->hist_depth > 0 && net->dims[NL] <= kFoldMaxOut) {
+    const long long wl = (long long)net->dims[NL] * net->ld[NL - 1];
+    net->off_wlast = off;
+    off += pad(wl);
+    net->off_mlast = off;
+    off += pad(wl);
+    net->off_zpart = off;
+    off += (long long)W * kLazyDotSlots * kFoldMaxOut;
+  }
   net->arena_doubles = off;
   return off;
 }
@@ -410,6 +420,7 @@ static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
   }
   p.lazy_depth = 0;
   p.prefetch_bytes = 0;
+  p.fold_out = 0;
   {
     static const long long env_ms = [] {
       const char *e = getenv("HPNN_SPIN_TIMEOUT_MS");

@@ -46,7 +46,8 @@ class DevNet(C.Structure):
                 ("off_cta_part", C.c_longlong * MAX_LAYERS), ("cta_slots", C.c_int),
                 ("off_hist_u", C.c_longlong * MAX_LAYERS), ("off_hist_v", C.c_longlong * MAX_LAYERS),
                 ("off_hist_dot", C.c_longlong * MAX_LAYERS),
-                ("hist_depth", C.c_int), ("off_panel", C.c_longlong), ("panel_stride", C.c_int)]
+                ("hist_depth", C.c_int), ("off_panel", C.c_longlong), ("panel_stride", C.c_int),
+                ("off_wlast", C.c_longlong), ("off_mlast", C.c_longlong), ("off_zpart", C.c_longlong)]
 
 
 _lib = None

@@ -182,6 +182,11 @@ typedef struct {
    * 2 buffers x 160 CTAs x panel_stride doubles (panel_stride = widest ld + 8; 0 = none) */
   long long off_panel;
   int panel_stride;
+  /* row-panel trainer, output layers of at most 32 neurons: the output layer is folded into the
+   * phases of the layer below it.  off_wlast / off_mlast: working copy of the WHOLE output layer
+   * (dims[n_layers] x ld[n_layers-1]) and of its momentum; off_zpart: per-(rank, CTA) partial
+   * output sums, world x 160 slots of 32 doubles.  0 = not reserved.                          */
+  long long off_wlast, off_mlast, off_zpart;
 } hpnn_dev_net;
 
 /* Deferred-update BP trainer for layers much larger than L2 (train_lazy.cu).  depth: write-back
