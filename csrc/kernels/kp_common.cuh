@@ -25,6 +25,7 @@ struct KP {
   hpnn_train_result *result;
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
+  int keep_l2;   // K-PL1: a rank's share of a layer fits L2, so the passes use caching loads instead of evict-first ones
   int fold_out;  // K-PL1: the output layer is folded into the phases of the layer below (see train_lazy1.cu)
   int fault;  // fault injection (tests): 1 = this rank leaves at kernel entry, as if its launch had failed
   unsigned long long spin_budget_ns;  // longest time any wait may take before the job is abandoned (0 = unbounded)

@@ -5,6 +5,18 @@
 
 namespace hpnn {
 
+// rows of layer l owned by rank q (the balanced split of kp_common.cuh), tabulated once per launch:
+// the consumers of per-(rank, CTA) slots ask "did CTA b of rank q produce anything" for hundreds of
+// slots per phase, and row0_of() is two 64-bit divisions (measured at 8 ranks: 3 us per gather).
+static __shared__ int s_rows_of[HPNN_MAX_LAYERS][HPNN_MAX_WORLD];
+__device__ __forceinline__ void rows_table_init(const hpnn_dev_net &n) {
+  for (int i = threadIdx.x; i < n.n_layers * n.world; i += blockDim.x) {
+    const int l = i / n.world, q = i % n.world;
+    s_rows_of[l][q] = row0_of(q + 1, n.dims[l + 1], n.world) - row0_of(q, n.dims[l + 1], n.world);
+  }
+  __syncthreads();
+}
+
 // block-wide sum of kLazyChunk values per thread; coef[j] (shared) = total for j < m, 0 otherwise.
 // Fixed order: lanes by butterfly, warps in index order.
 __device__ __forceinline__ void chunk_block_sum(double (&acc)[kLazyChunk], int m, double *coef, double *red) {
@@ -82,13 +94,12 @@ struct DotOut {
 // input x was produced by the previous row phase.  rows_prev(q) = rows of that phase on rank q.
 __device__ __forceinline__ void gather_dots(const hpnn_dev_net &n, int l, int m, double *coef, double *red, int grid) {
   const double *slots = n.arena[n.rank] + n.off_hist_dot[l];
-  const int N = n.dims[l];  // rows of layer l-1, split over the ranks
   double acc[kLazyChunk];
 #pragma unroll
   for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
   for (int idx = threadIdx.x; idx < n.world * kLazyDotSlots; idx += kThreads) {
     const int q = idx / kLazyDotSlots, b = idx % kLazyDotSlots;
-    const int rows_q = row0_of(q + 1, N, n.world) - row0_of(q, N, n.world);
+    const int rows_q = s_rows_of[l - 1][q];  // rows of layer l-1 on rank q
     if (b < grid && b < rows_q) chunk_fma(slots + (size_t)idx * kLazyChunk, 1.0, m, acc);
   }
   chunk_block_sum(acc, m, coef, red);

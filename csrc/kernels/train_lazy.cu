@@ -287,7 +287,8 @@ __device__ __forceinline__ void phase_rows_lazy(double *W, int ld, int rows, con
 __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy(const __grid_constant__ KP p) {
   extern __shared__ double smem[];
   watch_init(p);
-  if (p.fault == 1) return;  // injected fault: this rank never shows up
+  if (p.fault == 1) return;
+  rows_table_init(p.net);  // injected fault: this rank never shows up
   // xs doubles as the factor staging area of the write-back pass (the top-down phases read their
   // input vector from global memory), so it is at least kFlushStageDoubles long.  Keeping the
   // footprint at the plain trainer's size matters: 64 KB more shared memory shrank L1 enough to

@@ -85,45 +85,61 @@ constexpr int kPanelCols = 2 * kThreads;  // columns covered by one pass of the 
 
 // Read-only top-down pass over the own panel: four column chunks per thread, rows outermost, two
 // rows in flight.  Pout[c] = sum_i W[r0+i, c] * dsl[i].
+template <bool STREAM>
 __device__ __forceinline__ void panel_cols_read(const double *W, int ld, Panel pn, const double *dsl, double *Pout) {
+  // The (column group, row) pairs form ONE software-pipelined sequence, two items in flight: with a
+  // 7-row panel (8 ranks) a pipeline that restarted for every column group spent more time filling
+  // and draining than streaming.
   constexpr int G = 4;  // chunks per group
-  for (int g0 = 0; g0 < ld; g0 += G * kPanelCols) {
-    const int cbase = g0 + 2 * threadIdx.x;
-    double2 acc[G];
+  const int ng = (ld + G * kPanelCols - 1) / (G * kPanelCols);
+  const double2 zero2 = make_double2(0.0, 0.0);
+  double2 acc[G];
 #pragma unroll
-    for (int k = 0; k < G; ++k) acc[k] = make_double2(0.0, 0.0);
-    const double2 zero2 = make_double2(0.0, 0.0);
-    double2 wa[G], wb[G];
-    auto load = [&](double2 (&w)[G], int i) {
-      const double *row = W + (size_t)(pn.r0 + i) * ld;
-#pragma unroll
-      for (int k = 0; k < G; ++k) {
-        const int c = cbase + k * kPanelCols;
-        w[k] = (i < pn.cnt && c < ld) ? ldw2<true>(reinterpret_cast<const double2 *>(row + c)) : zero2;
-      }
-    };
-    auto consume = [&](double2 (&w)[G], int i) {
-      if (i < pn.cnt) {
-        const double d = dsl[i];
-#pragma unroll
-        for (int k = 0; k < G; ++k) {
-          acc[k].x = fma(w[k].x, d, acc[k].x);
-          acc[k].y = fma(w[k].y, d, acc[k].y);
-        }
-      }
-    };
-    load(wa, 0);
-    for (int i = 0; i < pn.cnt; i += 2) {
-      load(wb, i + 1);
-      consume(wa, i);
-      load(wa, i + 2);
-      consume(wb, i + 1);
-    }
+  for (int k = 0; k < G; ++k) acc[k] = zero2;
+  int lg = 0, li = 0;  // next item to load
+  int cg = 0, ci = 0;  // next item to consume
+  auto load_next = [&](double2 (&w)[G]) {
+    const bool on = lg < ng && pn.cnt > 0;
+    const int cbase = lg * G * kPanelCols + 2 * threadIdx.x;
+    const double *row = W + (size_t)(pn.r0 + li) * ld;
 #pragma unroll
     for (int k = 0; k < G; ++k) {
       const int c = cbase + k * kPanelCols;
-      if (c < ld) stg_cg2(reinterpret_cast<double2 *>(Pout + c), acc[k]);
+      w[k] = (on && c < ld) ? ldw2<STREAM>(reinterpret_cast<const double2 *>(row + c)) : zero2;
     }
+    if (++li >= pn.cnt) {
+      li = 0;
+      ++lg;
+    }
+  };
+  auto consume = [&](double2 (&w)[G]) {
+    if (cg >= ng) return;
+    const double d = dsl[ci];
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      acc[k].x = fma(w[k].x, d, acc[k].x);
+      acc[k].y = fma(w[k].y, d, acc[k].y);
+    }
+    if (++ci >= pn.cnt) {  // group complete
+      const int cbase = cg * G * kPanelCols + 2 * threadIdx.x;
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        const int c = cbase + k * kPanelCols;
+        if (c < ld) stg_cg2(reinterpret_cast<double2 *>(Pout + c), acc[k]);
+        acc[k] = zero2;
+      }
+      ci = 0;
+      ++cg;
+    }
+  };
+  double2 wa[G], wb[G];
+  const int total = ng * pn.cnt;
+  load_next(wa);
+  for (int t = 0; t < total; t += 2) {
+    load_next(wb);
+    consume(wa);
+    load_next(wa);
+    consume(wb);
   }
 }
 
@@ -294,23 +310,37 @@ __device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, cons
   const double2 zero2 = make_double2(0.0, 0.0);
   for (int i = lane; i < pn.cnt; i += 32) zpart[i * kZStride + warp] = 0.0;  // own slots only
   __syncwarp();
-  for (int g0 = 0; g0 < ld; g0 += G * kPanelCols) {
-    const int cbase = g0 + 2 * threadIdx.x;
+  // The loads of all (column group, row) pairs form one pipelined sequence (two rows in flight, running
+  // on into the next group); every group is padded to an even number of rows so that a row always
+  // sits in the same one of the two register buffers.
+  const int ng = (ld + G * kPanelCols - 1) / (G * kPanelCols);
+  const int cp = pn.cnt + (pn.cnt & 1);
+  int lg = 0, li = 0;  // next row to load
+  double2 wa[G], wb[G];
+  auto load_next = [&](double2 (&w)[G]) {
+    const bool on = lg < ng && li < pn.cnt;
+    const int cb = lg * G * kPanelCols + 2 * threadIdx.x;
+    const double *row = W + (size_t)(pn.r0 + li) * ld;
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      const int c = cb + k * kPanelCols;
+      w[k] = (on && c < ld) ? ldw2<false>(reinterpret_cast<const double2 *>(row + c)) : zero2;
+    }
+    if (++li >= cp) {
+      li = 0;
+      ++lg;
+    }
+  };
+  load_next(wa);
+  load_next(wb);
+  for (int g = 0; g < ng; ++g) {
+    const int cbase = g * G * kPanelCols + 2 * threadIdx.x;
     double2 xr[G];
 #pragma unroll
     for (int k = 0; k < G; ++k) {
       const int c = cbase + k * kPanelCols;
       xr[k] = (c < ld) ? *reinterpret_cast<const double2 *>(xs + c) : zero2;
     }
-    double2 wa[G], wb[G];
-    auto load = [&](double2 (&w)[G], int i) {
-      const double *row = W + (size_t)(pn.r0 + i) * ld;
-#pragma unroll
-      for (int k = 0; k < G; ++k) {
-        const int c = cbase + k * kPanelCols;
-        w[k] = (i < pn.cnt && c < ld) ? ldw2<false>(reinterpret_cast<const double2 *>(row + c)) : zero2;
-      }
-    };
     auto consume = [&](double2 (&w)[G], int i) -> double {
       double a = 0.0, b = 0.0;
       if (UPD && i < pn.cnt) {
@@ -333,16 +363,19 @@ __device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, cons
       }
       return a + b;
     };
-    load(wa, 0);
-    load(wb, 1);
-    for (int i0 = 0; i0 < pn.cnt; i0 += 8) {
+    for (int i0 = 0; i0 < cp; i0 += 8) {
       double pr[8];
 #pragma unroll
       for (int u = 0; u < 8; u += 2) {
-        pr[u] = consume(wa, i0 + u);
-        load(wa, i0 + u + 2);
-        pr[u + 1] = consume(wb, i0 + u + 1);
-        load(wb, i0 + u + 3);
+        if (i0 + u < cp) {
+          pr[u] = consume(wa, i0 + u);
+          load_next(wa);
+          pr[u + 1] = consume(wb, i0 + u + 1);
+          load_next(wb);
+        } else {
+          pr[u] = 0.0;
+          pr[u + 1] = 0.0;
+        }
       }
       const double s = reduce8(pr, lane);
       const int i = i0 + ((lane >> 2) & 7);
@@ -419,13 +452,12 @@ __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const do
 __device__ __forceinline__ void gather_dots_tagged(const hpnn_dev_net &n, int l, int m, unsigned long long tag,
                                                    double *coef, double *red, int grid) {
   const double *slots = n.arena[n.rank] + n.off_hist_dot[l];
-  const int N = n.dims[l];  // rows of layer l-1, split over the ranks
   double acc[kLazyChunk];
 #pragma unroll
   for (int j = 0; j < kLazyChunk; ++j) acc[j] = 0.0;
   for (int idx = threadIdx.x; idx < n.world * kLazyDotSlots; idx += kThreads) {
     const int q = idx / kLazyDotSlots, b = idx % kLazyDotSlots;
-    const int rows_q = row0_of(q + 1, N, n.world) - row0_of(q, N, n.world);
+    const int rows_q = s_rows_of[l - 1][q];
     if (b < grid && b < rows_q) {
       const double *addr[kLazyChunk];
       bool want[kLazyChunk];
@@ -452,6 +484,7 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   extern __shared__ double smem[];
   watch_init(p);
   if (p.fault == 1) return;  // injected fault: this rank never shows up
+  rows_table_init(p.net);
   const hpnn_dev_net &n = p.net;
   const int NL = n.n_layers;
   const int pmax = p.max_rows;  // here: widest panel, padded to 8 (see the launcher)
@@ -645,18 +678,29 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   // order: the same order on every CTA and every rank), then the usual statistics; dlast = all output deltas
   auto evaluate_fold = [&](double *o_out) -> OutStats {
     const double *zp = A + n.off_zpart;
-    const int lanes = n_out <= 16 ? 16 : 32, nparts = kThreads / lanes;
+    // thread = (output r, part): the valid slots (rank q, CTA bb < nb_q) are dealt to the parts
+    // round-robin in rank-major order, eight loads in flight per thread
+    const int lanes = n_out, nparts = kThreads / lanes;
     const int r = threadIdx.x % lanes, part = threadIdx.x / lanes;
-    const int nprev = n.dims[NL - 1];
     double s = 0.0;
     __syncthreads();
-#pragma unroll 4
-    for (int idx = part; idx < n.world * kLazyDotSlots; idx += nparts) {
-      const int q = idx / kLazyDotSlots, bb = idx % kLazyDotSlots;
-      const int rows_q = row0_of(q + 1, nprev, n.world) - row0_of(q, nprev, n.world);
-      if (bb < grid && bb < rows_q && r < n_out) s += ldg_cg(zp + (size_t)idx * kFoldMaxOut + r);
+    if (part < nparts) {
+      for (int q = 0; q < n.world; ++q) {
+        const int nbq = min(grid, s_rows_of[NL - 2][q]);
+        const double *base = zp + (size_t)q * kLazyDotSlots * kFoldMaxOut + r;
+        for (int b0 = part; b0 < nbq; b0 += 8 * nparts) {
+          double v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int bb = b0 + u * nparts;
+            v[u] = bb < nbq ? ldg_cg(base + (size_t)bb * kFoldMaxOut) : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) s += v[u];
+        }
+      }
+      red[part * lanes + r] = s;
     }
-    red[part * lanes + r] = s;
     __syncthreads();
     if ((int)threadIdx.x < n_out) {
       double z = 0.0;
@@ -744,7 +788,12 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
         const int gt = b * kThreads + threadIdx.x;
         for (int c = gt; c < n.ld[l]; c += grid * kThreads)
           stg_cg(HV + (size_t)c * kLazyChunk + m, tg ? h[c] : ldg_cg(h + c));
-        if (pn.cnt > 0) panel_cols_read(n.W[l], n.ld[l], pn, dsl, Pout);
+        if (pn.cnt > 0) {
+          // a layer share that fits L2 is read again soon (top-down of layer 1 -> its forward pass, forward
+          // of the top layer -> its top-down pass): keep it cached; otherwise stream with evict-first
+          if (p.keep_l2) panel_cols_read<false>(n.W[l], n.ld[l], pn, dsl, Pout);
+          else panel_cols_read<true>(n.W[l], n.ld[l], pn, dsl, Pout);
+        }
       } else if (pn.cnt > 0) {
         if (bpm) panel_cols_bpm<TG>(n.W[l], n.dW[l], n.ld[l], pn, dsl, h, p.lr, p.alpha, Pout);
         else panel_cols_flush<TG>(n.W[l], n.ld[l], pn, dsl, ul, HV, h, p.lr, m, Pout);
@@ -1009,6 +1058,16 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
       const char *e = getenv("HPNN_FOLD_OUT");
       return (e && !strcmp(e, "0")) ? 0 : 1;
     }();
+    static const int keep_env = [] {
+      const char *e = getenv("HPNN_L2_KEEP");
+      return e ? atoi(e) : -1;
+    }();
+    long long widest = 0;
+    for (int l = 1; l < n.n_layers; ++l) {
+      const long long bytes = 8LL * n.rows[l] * n.ld[l];
+      widest = bytes > widest ? bytes : widest;
+    }
+    p.keep_l2 = keep_env >= 0 ? (keep_env ? 1 : 0) : (widest <= (80LL << 20) ? 1 : 0);
     p.fold_out = (fold_env && !p.tagged && n.off_zpart > 0 && n.dims[n.n_layers] <= kFoldMaxOut && n.n_layers >= 3) ? 1 : 0;
   }
   p_out = p;
