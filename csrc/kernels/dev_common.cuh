@@ -79,6 +79,12 @@ __device__ __forceinline__ void multimem_st_f64(double *mc, double v) {
 __device__ __forceinline__ void multimem_st_u64(unsigned long long *mc, unsigned long long v) {
   asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
 }
+__device__ __forceinline__ void multimem_red_add_u64(unsigned long long *mc, unsigned long long v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_relaxed_sys_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ void multimem_red_add_f64(double *mc, double v) {
   asm volatile("multimem.red.relaxed.sys.global.add.f64 [%0], %1;" ::"l"(mc), "d"(v) : "memory");
 }

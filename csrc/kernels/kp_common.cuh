@@ -44,7 +44,8 @@ struct KP {
 //     consumed at its end: off the critical path) and leaves; hpnn_train_result.status = 1.
 // After an abort the weights, the barrier words and the tags of that sample are meaningless; the
 // host reports the error and must reset the sync state (hpnn_net does, HpnnNet.reset_sync()).
-constexpr int kAbortSlot = HPNN_MAX_WORLD;  // u64 index of the abort word in the arena's flag area
+constexpr int kAbortSlot = HPNN_MAX_WORLD;        // u64 index of the abort word in the arena's flag area
+constexpr int kCounterSlot = HPNN_MAX_WORLD + 1;  // ... and of the cross-rank barrier counter
 struct WatchState {
   unsigned long long *abort_word[HPNN_MAX_WORLD];  // [rank] is the local one
   int rank, world;
@@ -123,13 +124,14 @@ __device__ __forceinline__ unsigned long long watch_peek() {
 // at k+1 (ordered after the reset).  The barrier index survives kernel launches in
 // local_sync, so the rotation simply continues with the next sample.
 //
-// With several ranks CTA 0 alone watches the counter and publishes one flag word per rank over
-// NVLink (fence.sys + relaxed stores, or one multimem.st); every CTA polls the flag words of all
-// ranks in its own arena and issues one fence.sys.
-// local_sync words: [0],[32],[64] counters (own 128 B lines), [128] saved index, [160] launch id.
+// With several ranks CTA 0 alone watches the counter, then adds 1 to a barrier counter in every
+// rank's arena (fence.sys + one multimem.red, or a red per rank); every CTA polls the counter of
+// its own arena and ends with one acquire load.
+// local_sync words: [0],[32],[64] counters (own 128 B lines), [128] saved index, [129] cross-rank barrier count, [160] launch id.
 struct Barrier {
   unsigned *sync;
   unsigned k;     // barrier index, meaningful in thread 0
+  unsigned kx;    // number of cross-rank barriers so far (the arena's barrier counter reads world * kx)
   unsigned grid;  // CTAs of THIS rank (the whole grid, or the rank's share of a virtual-rank launch)
   int bid;        // index of this CTA within the rank
   __device__ __forceinline__ void init(const hpnn_dev_net &n, int grid_, int bid_) {
@@ -137,6 +139,7 @@ struct Barrier {
     grid = (unsigned)grid_;
     bid = bid_;
     k = (threadIdx.x == 0) ? ld_relaxed_gpu(sync + 128) : 0u;
+    kx = (threadIdx.x == 0) ? ld_relaxed_gpu(sync + 129) : 0u;
   }
   // grid barrier of this GPU only (no cross-rank part, no system-scope fences)
   __device__ __forceinline__ void sync_local() {
@@ -156,7 +159,10 @@ struct Barrier {
     __syncthreads();
   }
   __device__ __forceinline__ void finish() {  // call once, after the last barrier
-    if (bid == 0 && threadIdx.x == 0) sync[128] = k;
+    if (bid == 0 && threadIdx.x == 0) {
+      sync[128] = k;
+      sync[129] = kx;
+    }
   }
   // `remote`: this CTA stored into a peer's arena since the last barrier (only then does
   // it pay for a system-scope fence before arriving).
@@ -181,37 +187,32 @@ struct Barrier {
         if (bid == 0) *prev = 0;
         fence_gpu();
       } else {
-        // Several ranks.  CTA 0 alone watches the local counter and then publishes this rank's flag word
-        // (= barrier index) on EVERY rank, itself included: one multimem.st when the arenas have a
-        // multicast mapping, a store per rank otherwise.  Every CTA -- not only CTA 0 -- then polls the
-        // `world` flag words of its own arena directly (one 64-byte line): no relay through a "go" word.
-        const unsigned long long we = (unsigned long long)k;
+        // Several ranks.  CTA 0 alone watches the local counter, issues the ONE system-scope fence of the
+        // barrier and then adds 1 to the barrier counter of EVERY rank: a single multimem.red when the
+        // arenas have an NVLS multicast mapping (the switch applies it to all copies), one red per rank
+        // otherwise.  Every CTA -- not only CTA 0 -- polls the counter of its own arena (one word) until
+        // it reads world * barrier-index and finishes with one acquire load: no relay through CTA 0, no
+        // second fence.  (fence + red heads a release sequence that the other ranks' reds extend.)
+        ++kx;
+        const unsigned long long want = (unsigned long long)kx * (unsigned long long)n.world;
         if (bid == 0) {
           while (ld_relaxed_gpu(c) != grid) {
             if (sp.give_up()) break;
           }
           *prev = 0;
-          fence_sys();  // release: everything this rank wrote is visible before the flags
+          fence_sys();  // release: everything this rank wrote is visible before the counter moves
           if (n.arena_mc) {
-            multimem_st_u64(reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags) + n.rank, we);
+            multimem_red_add_u64(reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags) + kCounterSlot, 1ull);
           } else {
             for (int q = 0; q < n.world; ++q)
-              st_relaxed_sys(reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + n.rank, we);
+              red_add_relaxed_sys_u64(reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + kCounterSlot, 1ull);
           }
         }
-        const unsigned long long *mine = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags);
-        // relaxed polling, then ONE acquire load per flag word (it reads the release pattern's store or a
-        // later one): the peers' and the other local CTAs' stores are visible after it, without a
-        // second and third fence.sys on the critical path
-        unsigned long long seen = ~0ull;
-        for (int q = 0; q < n.world; ++q) {
-          while (ld_relaxed_sys(mine + q) < we) {
-            if (sp.give_up()) break;
-          }
-          const unsigned long long a = ld_acquire_sys(mine + q);
-          seen = a < seen ? a : seen;
+        const unsigned long long *ctr = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags) + kCounterSlot;
+        while (ld_relaxed_sys(ctr) < want) {
+          if (sp.give_up()) break;
         }
-        if (seen < we) s_watch.tripped = 1;  // only after a time-out
+        if (ld_acquire_sys(ctr) < want) s_watch.tripped = 1;  // only after a time-out
       }
     }
     __syncthreads();

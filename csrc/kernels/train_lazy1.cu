@@ -685,19 +685,24 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     double s = 0.0;
     __syncthreads();
     if (part < nparts) {
-      for (int q = 0; q < n.world; ++q) {
+      // all loads of all ranks' slots in flight at once (one L2 round trip for narrow output layers)
+      double v[HPNN_MAX_WORLD * 4];
+#pragma unroll
+      for (int q = 0; q < HPNN_MAX_WORLD; ++q) {
+        const int nbq = q < n.world ? min(grid, s_rows_of[NL - 2][q]) : 0;
+        const double *base = zp + (size_t)q * kLazyDotSlots * kFoldMaxOut + r;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int bb = part + u * nparts;
+          v[q * 4 + u] = bb < nbq ? ldg_cg(base + (size_t)bb * kFoldMaxOut) : 0.0;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < HPNN_MAX_WORLD * 4; ++j) s += v[j];
+      for (int q = 0; q < n.world; ++q) {  // wide output layers (few parts): the slots beyond four per part
         const int nbq = min(grid, s_rows_of[NL - 2][q]);
         const double *base = zp + (size_t)q * kLazyDotSlots * kFoldMaxOut + r;
-        for (int b0 = part; b0 < nbq; b0 += 8 * nparts) {
-          double v[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int bb = b0 + u * nparts;
-            v[u] = bb < nbq ? ldg_cg(base + (size_t)bb * kFoldMaxOut) : 0.0;
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) s += v[u];
-        }
+        for (int bb = part + 4 * nparts; bb < nbq; bb += nparts) s += ldg_cg(base + (size_t)bb * kFoldMaxOut);
       }
       red[part * lanes + r] = s;
     }
