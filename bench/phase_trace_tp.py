@@ -22,7 +22,7 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     nn_type, train, n_in, hid, n_out = CFG[name]
     k, _ = hp.generate_kernel(10958, n_in, hid, n_out)
-    eng = CudaEngine(k, nn_type, train, group=group, max_iter=iters, min_iter=iters + 10, delta=1e-300)
+    eng = CudaEngine(k, nn_type, train, group=group, split="always", max_iter=iters, min_iter=iters + 10, delta=1e-300)
     rng = np.random.default_rng(0)
     x = rng.random(n_in)
     t = np.full(n_out, 0.0 if nn_type == hp.TYPE_SNN else -1.0)

@@ -47,7 +47,7 @@ def main():
             continue
         group = dist.new_group(list(range(world)))  # collective over ALL ranks
         if rank < world:
-            eng = CudaEngine(k, nn_type, train, group=group if world > 1 else None, max_iter=iters, min_iter=iters + 10,
+            eng = CudaEngine(k, nn_type, train, group=group if world > 1 else None, split="always", max_iter=iters, min_iter=iters + 10,
                              delta=1e-300)
             for proto in protos if world > 1 else ["single"]:
                 if world > 1:

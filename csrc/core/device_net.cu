@@ -126,6 +126,20 @@ hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gp
   }
   if (n_gpus <= 0 || n_gpus > avail) n_gpus = avail;
   if (n_gpus > HPNN_MAX_WORLD) n_gpus = HPNN_MAX_WORLD;
+  if (n_gpus > 1) {
+    // Row-splitting pays only when streaming the weights dominates an iteration.  Measured on 8 B200:
+    // 784-8192x4-10 (1.6 GB) runs 3.3x faster on 8 GPUs, but SNN 784-1000-1000-10 (14 MB) and the
+    // 851-230-230 tutorial net (1.6 MB) take ~38 / ~23 us per iteration at 2..8 ranks against 20 / 12 us
+    // on one GPU: their iterations are a chain of ~10 dependent hand-overs, and one that crosses NVLink
+    // (~2 us) costs several times one that stays in one GPU's L2 (~0.5 us), whatever the protocol
+    // (profiles/r2_probe8_small.jsonl).  Below HPNN_TP_MIN_MB (default 128 MB of weights) the net
+    // therefore stays on ONE GPU even when more are visible.
+    long long bytes = 0;
+    for (size_t l = 0; l + 1 < k->dims.size(); ++l) bytes += 8LL * k->dims[l] * k->dims[l + 1];
+    const char *e = getenv("HPNN_TP_MIN_MB");
+    const long long min_mb = e ? atoll(e) : 128;
+    if (bytes < (min_mb << 20)) n_gpus = 1;
+  }
   hpnn_net *n = new hpnn_net();
   n->type = type;
   n->world = n_gpus;

@@ -152,10 +152,19 @@ class CudaEngine:
 
     def __init__(self, kernel: Kernel, nn_type: int, train: int, lr: Optional[float] = None, alpha: float = 0.2,
                  delta: float = -1.0, min_iter: int = -1, max_iter: int = -1, stable_softmax: bool = False,
-                 group=None, device=None, **_):
+                 group=None, device=None, split: str = "auto", **_):
         from .models.net import HpnnNet
 
         self.type, self.train_kind = nn_type, train
+        # Row-splitting pays only when streaming the weights dominates an iteration (1.6 GB net: 3.3x on 8
+        # GPUs; 14 MB and 1.6 MB nets: ~2x SLOWER on 2..8 GPUs than on one, every hand-over that crosses
+        # NVLink costs several L2 hand-overs, profiles/r2_probe8_small.jsonl).  split="auto": below
+        # HPNN_TP_MIN_MB (default 128 MB of weights) every rank trains a full replica on its own GPU (all
+        # ranks see the same samples, so the replicas stay identical); "always" / "never" force it.
+        if group is not None and split != "always":
+            nbytes = 8 * sum(a * b for a, b in zip(kernel.dims[:-1], kernel.dims[1:]))
+            if split == "never" or nbytes < (int(os.environ.get("HPNN_TP_MIN_MB", "128")) << 20):
+                group = None
         self.net = HpnnNet(kernel, nn_type, device=device, momentum=(train == N.TRAIN_BPM), group=group)
         self.opts = self.net.make_opts(train, lr, alpha, delta, min_iter, max_iter, stable_softmax)
         self.stable = stable_softmax

@@ -42,7 +42,7 @@ def main():
         k, _ = hp.generate_kernel(77, n_in, hid, n_out)
         X, T = problem(nn_type, n_in, n_out, 3, 11)
         kw = dict(max_iter=400)
-        fused = CudaEngine(k, nn_type, train, group=group, **kw)
+        fused = CudaEngine(k, nn_type, train, group=group, split="always", **kw)
         if rank == 0 and n_in == 64:
             sy = fused.net._symm
             print(f"case symmetric-memory backend={sy.backend} multicast={'yes' if sy.mc_ptr else 'no'} world={world}", flush=True)
@@ -92,7 +92,7 @@ def main():
             X, T = problem(nn_type, 72, 10, 2, 17)
             for n_it in (5, 19):
                 kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
-                lazy = CudaEngine(k, nn_type, N.TRAIN_BP, group=group, **kw)
+                lazy = CudaEngine(k, nn_type, N.TRAIN_BP, group=group, split="always", **kw)
                 assert lazy.net.net.hist_depth == 8
                 cpu = CpuEngine(k, nn_type, N.TRAIN_BP, cuda_defaults=True, **kw) if rank == 0 else None
                 e_err = 0.0

@@ -64,7 +64,7 @@ def test_c_driver_row_splits_over_all_gpus(tmp_path, n_gpus):
     arts = B.build(verbose=False)
     d = _setup(tmp_path, "SNN", "BPM")
     vis = ",".join(str(i) for i in range(n_gpus))
-    out, rows_n, k_n = _train(arts["train_nn"], d, {"CUDA_VISIBLE_DEVICES": vis})
+    out, rows_n, k_n = _train(arts["train_nn"], d, {"CUDA_VISIBLE_DEVICES": vis, "HPNN_TP_MIN_MB": "0"})  # force the split
     assert f"CUDA started, found {n_gpus} GPU(s)" in out
     _, rows_1, k_1 = _train(arts["train_nn"], d, {"CUDA_VISIBLE_DEVICES": "0"})
     for (_, a), (_, b) in zip(rows_n, rows_1):
