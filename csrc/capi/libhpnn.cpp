@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <unistd.h>
 
 #include <mutex>
 #include <string>
@@ -62,6 +63,7 @@ void unregister_shim(Shim *s) {
 }
 
 int g_gpu_cap = 0;          // nn_set_n_gpu: 0 = all
+int g_first_dev = 0;        // one process per GPU (torchrun / mpirun): this process's device
 bool g_cuda_ready = false;  // nn_init_CUDA succeeded
 
 bool use_device() {
@@ -155,7 +157,7 @@ hpnn_net *device_for(Shim *s, int type, bool momentum) {
     drop_device(s);
   }
   if (!s->dev) {
-    s->dev = hpnn_net_create(s->host, type, momentum, want_gpus);
+    s->dev = hpnn_net_create_on(s->host, type, momentum, want_gpus, g_first_dev);
     if (!s->dev) {
       NN_WARN(stderr, "device engine unavailable (%s): using the CPU engine\n", hpnn_last_error());
       return nullptr;
@@ -263,6 +265,62 @@ std::vector<std::string> listed_files(const char *dir) {
   return v;
 }
 
+// ---- several processes started by torchrun / mpirun / srun (the reference's MPI build, src/libhpnn.c:
+// 182-200, src/ann.c:242-245, 549-614): rank-0-only output and file writing, ONE GPU per process, and
+// every rank ends up with the same kernel.  The reference broadcasts the kernel rank 0 read or
+// generated; here every rank reads the same file / draws the same glibc random() stream, so only the
+// seed has to be agreed on when the configuration says "0 = pick one" (rank 0 picks, the others read
+// it from a file named after the launcher's process id, which all local ranks share).
+int env_int(const char *const *keys, int n_keys, int fallback) {
+  for (int i = 0; i < n_keys; ++i) {
+    const char *v = getenv(keys[i]);
+    if (v && *v) return atoi(v);
+  }
+  return fallback;
+}
+int launcher_world() {
+  static const char *k[] = {"WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE", "SLURM_NTASKS"};
+  return env_int(k, 4, 1);
+}
+int launcher_rank() {
+  static const char *k[] = {"RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK", "SLURM_PROCID"};
+  return env_int(k, 4, 0);
+}
+int launcher_local_rank() {
+  static const char *k[] = {"LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MPI_LOCALRANKID", "SLURM_LOCALID"};
+  return env_int(k, 4, launcher_rank());
+}
+unsigned agreed_seed(unsigned seed) {
+  if (seed != 0 || launcher_world() < 2) return seed ? seed : (unsigned)time(NULL);
+  static unsigned serial = 0;  // several "pick one" requests per run: one file each
+  char path[256];
+  snprintf(path, sizeof(path), "/tmp/.hpnn_seed_%ld_%u", (long)getppid(), serial++);
+  if (launcher_rank() == 0) {
+    const unsigned s = (unsigned)time(NULL);
+    char tmp[280];
+    snprintf(tmp, sizeof(tmp), "%s.tmp", path);
+    FILE *fp = fopen(tmp, "w");
+    if (fp) {
+      fprintf(fp, "%u\n", s);
+      fclose(fp);
+      rename(tmp, path);
+    }
+    return s;
+  }
+  for (int tries = 0; tries < 3000; ++tries) {  // up to 30 s
+    FILE *fp = fopen(path, "r");
+    unsigned s = 0;
+    if (fp) {
+      const int got = fscanf(fp, "%u", &s);
+      fclose(fp);
+      if (got == 1 && s != 0) return s;
+    }
+    usleep(10000);
+  }
+  NN_WARN(stderr, "rank %i: no seed from rank 0, using the clock\n", launcher_rank());
+  return (unsigned)time(NULL);
+}
+
 }  // namespace
 
 extern "C" {
@@ -300,8 +358,7 @@ void nn_toggle_dry() { lib_runtime.nn_dry = !lib_runtime.nn_dry; }  // the refer
 
 nn_cap nn_return_capabilities() {
   unsigned res = NN_CAP_OMP;
-  const char *ws = getenv("WORLD_SIZE");
-  if (ws && atoi(ws) > 1) res |= NN_CAP_MPI;
+  if (launcher_world() > 1) res |= NN_CAP_MPI;
   if (hpnn_cuda_device_count() > 0) res |= NN_CAP_CUDA;
   return (nn_cap)res;
 }
@@ -326,12 +383,11 @@ BOOL nn_init_OMP() {
   return TRUE;
 }
 BOOL nn_init_MPI() {
-  const char *ws = getenv("WORLD_SIZE");
-  if (!ws || atoi(ws) < 2) {
+  if (launcher_world() < 2) {
     NN_WARN(stdout, "failed to init MPI (no capability).\n");
     return FALSE;
   }
-  lib_runtime.nn_num_tasks = (UINT)atoi(ws);
+  lib_runtime.nn_num_tasks = (UINT)launcher_world();
   NN_OUT(stdout, "MPI started %i tasks.\n", lib_runtime.nn_num_tasks);
   return TRUE;
 }
@@ -341,6 +397,20 @@ BOOL nn_init_CUDA() {
     NN_WARN(stderr, "CUDA error: no CUDA-capable device reported.\n");
     g_cuda_ready = false;
     return FALSE;
+  }
+  if (launcher_world() > 1) {
+    // one process per GPU: this rank drives device (local rank mod devices) and nothing else; the
+    // ranks do not split a net between them (each holds the whole net on its GPU, all train the
+    // same samples), which is what the reference's MPI + CUDA combination amounts to as well
+    // (its device code bypasses MPI, src/ann.c:893-896)
+    g_first_dev = launcher_local_rank() % n;
+    hpnn_cuda_set_device(g_first_dev);
+    lib_runtime.cudas.n_gpu = 1;
+    NN_WARN(stdout, "CUDA started, found %i GPU(s).\n", n);
+    NN_OUT(stdout, "task %i of %i uses GPU[%i].\n", launcher_rank(), launcher_world(), g_first_dev);
+    lib_runtime.cudas.mem_model = CUDA_MEM_NONE;
+    g_cuda_ready = true;
+    return TRUE;
   }
   lib_runtime.cudas.n_gpu = (UINT)n;
   NN_WARN(stdout, "CUDA started, found %i GPU(s).\n", n);
@@ -399,9 +469,8 @@ BOOL nn_get_mpi_tasks(UINT *n) {
   return (lib_runtime.capability & NN_CAP_MPI) ? TRUE : FALSE;
 }
 BOOL nn_get_curr_mpi_task(UINT *task) {
-  const char *r = getenv("RANK");
-  if (!(lib_runtime.capability & NN_CAP_MPI) || !r) return FALSE;
-  *task = (UINT)atoi(r);
+  if (!(lib_runtime.capability & NN_CAP_MPI)) return FALSE;
+  *task = (UINT)launcher_rank();
   return TRUE;
 }
 BOOL nn_set_n_gpu(UINT n) {
@@ -613,7 +682,7 @@ BOOL nn_train_kernel(nn_def *c) {
     return FALSE;
   }
   closedir(probe);
-  if (c->seed == 0) c->seed = (UINT)time(NULL);
+  if (c->seed == 0) c->seed = (UINT)agreed_seed(0);
   std::vector<int> order(files.size());
   hpnn_shuffle_order(c->seed, (int)files.size(), order.data());
   for (int idx : order) {
@@ -685,7 +754,7 @@ void nn_run_kernel(nn_def *c) {
   }
   closedir(probe);
   std::vector<std::string> files = listed_files(c->tests);
-  if (c->seed == 0) c->seed = (UINT)time(NULL);
+  if (c->seed == 0) c->seed = (UINT)agreed_seed(0);
   std::vector<int> order(files.size());
   hpnn_shuffle_order(c->seed, (int)files.size(), order.data());
   const int type = c->type == NN_TYPE_SNN ? HPNN_TYPE_SNN : HPNN_TYPE_ANN;
@@ -801,7 +870,7 @@ kernel_ann *ann_generate(UINT *seed, UINT n_inputs, UINT n_hiddens, UINT n_outpu
   dims.push_back((int)n_inputs);
   for (UINT i = 0; i < n_hiddens; ++i) dims.push_back((int)hiddens[i]);
   dims.push_back((int)n_outputs);
-  unsigned s0 = seed ? *seed : 0;
+  unsigned s0 = agreed_seed(seed ? *seed : 0);  // several processes: rank 0's choice when the seed is 0
   Shim *s = wrap(hpnn_kernel_generate(&s0, (int)dims.size(), dims.data()));
   if (seed) *seed = s0;
   return s ? s->pub : NULL;

@@ -111,6 +111,10 @@ int hpnn_net_download(hpnn_net *n, hpnn_kernel *k) {
 }
 
 hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gpus) {
+  return hpnn_net_create_on(k, type, momentum, n_gpus, 0);
+}
+
+hpnn_net *hpnn_net_create_on(const hpnn_kernel *k, int type, int momentum, int n_gpus, int first_dev) {
   if (!k) return nullptr;
   int avail = 0;
   if (cudaGetDeviceCount(&avail) != cudaSuccess || avail < 1) {
@@ -124,6 +128,8 @@ hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gp
     hpnn::set_error_msg("hpnn_net_create: more than HPNN_MAX_LAYERS weight layers (CPU engine only)");
     return nullptr;
   }
+  if (first_dev < 0 || first_dev >= avail) first_dev = 0;
+  avail -= first_dev;
   if (n_gpus <= 0 || n_gpus > avail) n_gpus = avail;
   if (n_gpus > HPNN_MAX_WORLD) n_gpus = HPNN_MAX_WORLD;
   if (n_gpus > 1) {
@@ -151,13 +157,13 @@ hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gp
   // peer access all-to-all (the reference only enables it towards GPU 0, src/libhpnn.c:282-288)
   for (int a = 0; a < n_gpus && ok; ++a)
     for (int b = 0; b < n_gpus && ok; ++b)
-      if (a != b && hpnn_enable_peer_access(a, b) != 0) {
+      if (a != b && hpnn_enable_peer_access(first_dev + a, first_dev + b) != 0) {
         hpnn::set_error_msg("hpnn_net_create: GPUs cannot reach each other (peer access)");
         ok = false;
       }
   for (int g = 0; g < n_gpus && ok; ++g) {
     auto &r = n->ranks[g];
-    r.dev = g;
+    r.dev = first_dev + g;
     cudaSetDevice(g);
     memset(&r.net, 0, sizeof(r.net));
     r.net.n_layers = NL;
@@ -219,7 +225,7 @@ hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gp
     cudaSetDevice(r.dev);
     cudaDeviceSynchronize();
   }
-  cudaSetDevice(0);
+  cudaSetDevice(first_dev);
   if (!ok) {
     hpnn_net_destroy(n);
     return nullptr;

@@ -332,6 +332,9 @@ int hpnn_dev_grad_merge(double *W, long long n, double *const *grads, int n_rank
  * per GPU per sample, collectives issued from inside the kernels over peer memory). */
 typedef struct hpnn_net hpnn_net;
 hpnn_net *hpnn_net_create(const hpnn_kernel *k, int type, int momentum, int n_gpus);
+/* same, on devices first_dev .. first_dev + n_gpus - 1 (one process per GPU under torchrun / mpirun:
+ * first_dev = the local rank, n_gpus = 1) */
+hpnn_net *hpnn_net_create_on(const hpnn_kernel *k, int type, int momentum, int n_gpus, int first_dev);
 void hpnn_net_destroy(hpnn_net *n);
 int hpnn_net_world(const hpnn_net *n);
 void hpnn_net_set_type(hpnn_net *n, int type);

@@ -323,3 +323,38 @@ def test_model_layer_caller_allocated_kernel(artefacts, tmp_path):
     r = _run([str(exe)], tmp_path)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     assert "MODEL_LAYER_OK" in r.stdout
+
+
+def test_c_driver_under_a_multi_process_launcher(artefacts, tmp_path):
+    """Several processes as torchrun / mpirun start them: only rank 0 prints and writes
+    kernel files, every rank ends with the same kernel (here: a seed of 0 is agreed on through rank 0),
+    and nn_get_mpi_tasks / nn_get_curr_mpi_task report the launcher's numbers."""
+    import threading
+
+    d = _golden_dir(tmp_path)
+    write_conf(d / "nn.conf", seed=0)  # "pick a seed": the ranks must not pick different ones
+    dirs, outs = [], {}
+    for r in range(3):
+        rd = tmp_path / f"rank{r}"
+        rd.mkdir()
+        for sub in ("samples", "tests"):
+            os.symlink(d / sub, rd / sub)
+        (rd / "nn.conf").write_text((d / "nn.conf").read_text())
+        dirs.append(rd)
+
+    def run(r):
+        env = {"WORLD_SIZE": "3", "RANK": str(r), "LOCAL_RANK": str(r)}
+        outs[r] = _run([str(artefacts["train_nn"]), "-v", "-v", "nn.conf"], dirs[r], env)
+
+    ts = [threading.Thread(target=run, args=(r,)) for r in range(3)]  # same parent pid, like launcher workers
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert all(outs[r].returncode == 0 for r in range(3)), [outs[r].stderr for r in range(3)]
+    assert outs[0].stdout.count("TRAINING FILE") == 6
+    seed_file = "/tmp/.hpnn_seed_%d_0" % os.getpid()  # rank 0 published its choice for the others
+    assert os.path.exists(seed_file) and int(open(seed_file).read()) > 0
+    os.remove(seed_file)
+    assert outs[1].stdout.strip() == "" and outs[2].stdout.strip() == ""  # rank-0-only output
+    assert (dirs[0] / "kernel.opt").exists() and not (dirs[1] / "kernel.opt").exists()
