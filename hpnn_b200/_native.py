@@ -129,6 +129,9 @@ def _declare(lib):
         "hpnn_dev_world_barrier": (i, [C.POINTER(vp), i, i, C.c_ulonglong, vp]),
         "hpnn_dev_grad_merge": (i, [vp, ll, C.POINTER(vp), i, d, vp]),
         "hpnn_dev_launch_count": (ll, [i]),
+        "hpnn_dev_dp_publish": (i, [vp, ll, C.POINTER(vp), vp, C.POINTER(vp), vp, i, C.c_ulonglong, vp]),
+        "hpnn_dev_dp_apply": (i, [vp, i, i, i, vp, ll, vp, ll, i, vp, C.c_ulonglong, ll, vp, vp]),
+        "hpnn_dev_grad_merge_nvls": (i, [vp, vp, vp, ll, i, i, d, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

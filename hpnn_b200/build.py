@@ -38,6 +38,7 @@ CORE_SOURCES = [
     "csrc/kernels/train_lazy1.cu",
     "csrc/kernels/ops.cu",
     "csrc/kernels/gemm_umma.cu",
+    "csrc/kernels/dp_merge.cu",
     "csrc/kernels/noalloc.cu",
 ]
 SHIM_SOURCES = ["csrc/capi/libhpnn.cpp"]

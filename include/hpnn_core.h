@@ -324,6 +324,24 @@ int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void
 int hpnn_dev_grad_merge(double *W, long long n, double *const *grads, int n_ranks, double scale,
                         void *stream);
 
+/* Factored form of the same merge (csrc/kernels/dp_merge.cu): a BP update is lr*delta (x) h, so the
+ * ranks exchange the FACTORS (O(N+M) per layer) instead of gradient matrices (O(N*M)).
+ * dp_publish copies `n` doubles into this rank's slot of every rank's factor buffer (dst_all[q], or one
+ * multimem.st per element through dst_mc when non-NULL), then fence.sys and sets this rank's step flag
+ * on every rank.  dp_apply waits on the device until flags[0..world) >= step (timeout_ms > 0: gives up,
+ * leaves W untouched and sets *status_dev = 1) and adds sum_r U[r*u_stride + i] * V[r*v_stride + j] to
+ * W[i][j], ranks in index order.  grad_merge_nvls is the matrix form through NVLS: rank r reduces slice
+ * r of all gradient buffers with multimem.ld_reduce and writes the new weights into every replica with
+ * multimem.st (W_mc / G_mc: multicast addresses from hpnn_symm_mc_ptr).  No reference counterpart. */
+int hpnn_dev_dp_publish(const double *src, long long n, double *const *dst_all, double *dst_mc,
+                        unsigned long long *const *flag_all, unsigned long long *flag_mc, int world,
+                        unsigned long long step, void *stream);
+int hpnn_dev_dp_apply(double *W, int ld, int rows, int cols, const double *U, long long u_stride, const double *V,
+                      long long v_stride, int world, const unsigned long long *flags, unsigned long long step,
+                      long long timeout_ms, int *status_dev, void *stream);
+int hpnn_dev_grad_merge_nvls(const double *W_local, double *W_mc, const double *G_mc, long long n, int rank, int world,
+                             double scale, void *stream);
+
 /* ------------------------------------------------------------------------ */
 /* hpnn_net: device-resident network driven from one host process            */
 /* ------------------------------------------------------------------------ */

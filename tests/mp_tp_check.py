@@ -118,12 +118,17 @@ def main():
 
     k, _ = hp.generate_kernel(5, 50, [30, 20], 6)
     X, T = problem(N.TYPE_ANN, 50, 6, world * 3, 3)
-    a = DataParallelTrainer(k, N.TYPE_ANN, lr=0.01, group=group, merge="fused")
-    b = DataParallelTrainer(k, N.TYPE_ANN, lr=0.01, group=group, merge="nccl")
+    modes = ["factored", "fused", "nccl"]
+    probe = DataParallelTrainer(k, N.TYPE_ANN, lr=0.01, group=group, merge="factored")
+    have_mc = bool(probe.fbuf.mc_ptr)
+    probe.close()
+    if have_mc:
+        modes.append("nvls")
+    trainers = {m: DataParallelTrainer(k, N.TYPE_ANN, lr=0.01, group=group, merge=m) for m in modes}
     Wser = [torch.from_numpy(w.copy()).cuda() for w in k.weights]
     for s in range(3):
-        a.step(X[s * world + rank], T[s * world + rank])
-        b.step(X[s * world + rank], T[s * world + rank])
+        for tr in trainers.values():
+            tr.step(X[s * world + rank], T[s * world + rank])
         upd = [torch.zeros_like(w) for w in Wser]
         for r in range(world):  # serial reference: sum of the per-sample updates from the same weights
             xs = torch.from_numpy(X[s * world + r]).cuda(); ts = torch.from_numpy(T[s * world + r]).cuda()
@@ -132,13 +137,20 @@ def main():
                 upd[l] += torch.outer(0.01 * d[l], acts[l])
         for l in range(len(Wser)):
             Wser[l] += upd[l]
-    e_ab = max(float((x - y).abs().max()) for x, y in zip(a.W, b.W))
-    e_as = max(float((x - y).abs().max()) for x, y in zip(a.W, Wser))
+    trainers["factored"].check()
+    errs = {m: max(float((x - y).abs().max()) for x, y in zip(tr.W, Wser)) for m, tr in trainers.items()}
+    # replicas must be bit-identical across ranks (no broadcast ever happens)
+    flat = trainers["factored"].flat.clone()
+    ref0 = flat.clone()
+    dist.broadcast(ref0, src=0)
+    same = float((flat - ref0).abs().max())
     if rank == 0:
-        print(f"case dp-merge world={world}: max|fused-nccl|={e_ab:.2e} max|fused-serial|={e_as:.2e}", flush=True)
-    if not (e_ab < 1e-13 and e_as < 1e-13):
+        print(f"case dp-merge world={world} multicast={'yes' if have_mc else 'no'}: " +
+              " ".join(f"max|{m}-serial|={e:.2e}" for m, e in errs.items()) + f" replica spread={same:.1e}", flush=True)
+    if not (max(errs.values()) < 1e-13 and same == 0.0):
         fails += 1
-    a.close(); b.close()
+    for tr in trainers.values():
+        tr.close()
     # ---- batched inference on the row-split net: fused GEMM+all-gather == NCCL == single-rank
     from hpnn_b200.models.net import HpnnNet
     from hpnn_b200.parallel.tp import TPBatchRunner, forward_batch_parallel
