@@ -27,7 +27,7 @@ def help_text(prog: str, train: bool) -> str:
 
 
 def parse(argv: List[str], prog: str, train: bool):
-    opts = {"omp": None, "blas": None, "streams": 1, "dry": False, "backend": None, "lr": None, "batch": 0,
+    opts = {"omp": None, "blas": None, "streams": 1, "dry": False, "backend": None, "lr": None, "batch": -1,
             "conf": None, "help": False}
     i = 1
 
