@@ -30,13 +30,13 @@ namespace umma {
 
 constexpr int BM = 128, BN = 128, BK = 64;       // tile (BK bf16 = one 128-byte swizzle row)
 constexpr int UMMA_K = 16;                       // bf16 MMA depth
-constexpr int STAGES = 3;                        // 3 x 32 KB: two CTAs fit one SM, so one CTA's
-                                                 // epilogue overlaps the other's MMA main loop
+constexpr int STAGES = 5;                        // 5 x 32 KB ring, one persistent CTA per SM
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;   // 32 KB
-constexpr int TMEM_COLS = 128;
+constexpr int TMEM_COLS = 256;                   // two 128-column fp32 accumulators
 constexpr int THREADS = 192;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int OUT_BYTES = BM * BN * 2;           // bf16 output tile staged for the TMA store (32 KB)
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -107,30 +107,55 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 // instruction descriptor: D=f32, A=B=bf16, both K-major, N=128, M=128
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
-__global__ void __launch_bounds__(THREADS, 2)
-    k_gemm_bf16_umma(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w, int batch,
-                     int rows, int k_total, double *__restrict__ Y, int ldy, int act_kind) {
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *map, const void *smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }  // the 4 epilogue warps
+
+// Persistent kernel: CTA c works on output tiles c, c + gridDim.x, ...  Two 128-column accumulators in
+// TMEM: while the epilogue warps drain tile i (tcgen05.ld, activation, store) the MMA warp already
+// accumulates tile i+1, and the TMA producer runs ahead through the shared-memory ring across tile
+// boundaries.  OUT_BF16: hidden layers hand bf16 activations straight to the next layer's GEMM -- the tile is
+// staged in shared memory in the 128-byte-swizzle layout (conflict-free 16-byte stores) and leaves
+// through two TMA stores; otherwise FP64 results are stored directly (the last layer, 10..230 wide).
+template <bool OUT_BF16>
+__global__ void __launch_bounds__(THREADS, 1)
+    k_gemm_bf16_umma(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                     const __grid_constant__ CUtensorMap map_y, int batch, int rows, int k_total, double *__restrict__ Y,
+                     int ldy, int act_kind) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * STAGE_BYTES);
-  uint64_t *full = bars, *empty = bars + STAGES, *tmem_full = bars + 2 * STAGES;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * STAGES + 1);
+  uint8_t *stage_out = smem + STAGES * STAGE_BYTES;  // 2 x [128 rows x 128 B] (OUT_BF16 only)
+  uint64_t *bars = reinterpret_cast<uint64_t *>(stage_out + OUT_BYTES);
+  uint64_t *full = bars, *empty = bars + STAGES, *tmem_full = bars + 2 * STAGES, *tmem_empty = tmem_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
   const int nk = (k_total + BK - 1) / BK;
+  const int ntn = (rows + BN - 1) / BN, ntm = (batch + BM - 1) / BM;
+  const int ntiles = ntn * ntm;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_w)) : "memory");
+    if (OUT_BF16) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_y)) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], 4);  // one arrival per epilogue warp
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) {  // whole warp: TMEM allocation
+  if (warp == 1) {  // whole warp: TMEM allocation (two accumulators)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                  "r"((uint32_t)TMEM_COLS)
                  : "memory");
@@ -142,58 +167,116 @@ __global__ void __launch_bounds__(THREADS, 2)
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t ph = (kb / STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        mbar_expect_tx(&full[s], STAGE_BYTES);
-        uint8_t *a = smem + s * STAGE_BYTES;
-        tma_load_2d(a, &map_x, &full[s], kb * BK, m0);
-        tma_load_2d(a + A_BYTES, &map_w, &full[s], kb * BK, n0);
+    if (lane == 0) {  // TMA producer: one ring for all tiles of this CTA
+      int it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int m0 = (t / ntn) * BM, n0 = (t % ntn) * BN;
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_expect_tx(&full[s], STAGE_BYTES);
+          uint8_t *a = smem + s * STAGE_BYTES;
+          tma_load_2d(a, &map_x, &full[s], kb * BK, m0);
+          tma_load_2d(a + A_BYTES, &map_w, &full[s], kb * BK, n0);
+        }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t ph = (kb / STAGES) & 1;
-        mbar_wait(&full[s], ph);
+    if (lane == 0) {  // MMA issuer
+      int it = 0, i = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
+        const int acc = i & 1;
+        mbar_wait(&tmem_empty[acc], ((i >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t a_addr = smem_u32(smem + s * STAGE_BYTES);
-        const uint64_t adesc = smem_desc_sw128(a_addr), bdesc = smem_desc_sw128(a_addr + A_BYTES);
+        const uint32_t d = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < nk; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&full[s], ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_addr = smem_u32(smem + s * STAGE_BYTES);
+          const uint64_t adesc = smem_desc_sw128(a_addr), bdesc = smem_desc_sw128(a_addr + A_BYTES);
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          // advancing K inside the swizzle atom = +32 bytes on the start address field
-          umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), kIdesc, (kb | k) ? 1u : 0u);
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advancing K inside the swizzle atom = +32 bytes on the start address field
+            umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), kIdesc, (kb | k) ? 1u : 0u);
+          }
+          umma_commit(&empty[s]);                          // slot reusable once these MMAs have read it
+          if (kb == nk - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
         }
-        umma_commit(&empty[s]);                   // slot reusable once these MMAs have read it
-        if (kb == nk - 1) umma_commit(tmem_full); // accumulator complete
       }
     }
   } else {
     // epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31
     const int q = warp & 3;
-    mbar_wait(tmem_full, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int b = m0 + q * 32 + lane;
+    const int et = threadIdx.x - 64;  // 0..127
+    int i = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
+      const int m0 = (t / ntn) * BM, n0 = (t % ntn) * BN;
+      const int acc = i & 1;
+      mbar_wait(&tmem_full[acc], (i >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int r = q * 32 + lane;  // row of the tile held by this thread
+      if (OUT_BF16) {
+        if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
+        epi_bar();
+      }
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-      if (b < batch) {
-        double *yrow = Y + (size_t)b * ldy;
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c0), v);
+        if (c0 == BN - 32) {  // everything of this accumulator is in registers: hand it back to the MMA warp
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
+        if (OUT_BF16) {
+          // 128-byte-swizzle layout of a [128 x 64] bf16 box: 16-byte chunk j of row r sits at chunk j ^ (r & 7)
+          uint8_t *box = stage_out + (c0 >> 6) * (BM * 128) + r * 128;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = n0 + c0 + j;
-          if (n < rows) {
-            // reduced-precision path: the activation is evaluated in fp32 (operands were bf16)
-            const float z = __uint_as_float(v[j]);
-            yrow[n] = (double)(act_kind == 0 ? __fdividef(2.0f, 1.0f + __expf(-z)) - 1.0f : z);
+          for (int j = 0; j < 4; ++j) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float z0 = __uint_as_float(v[j * 8 + 2 * e]), z1 = __uint_as_float(v[j * 8 + 2 * e + 1]);
+              if (act_kind == 0) {
+                z0 = __fdividef(2.0f, 1.0f + __expf(-z0)) - 1.0f;
+                z1 = __fdividef(2.0f, 1.0f + __expf(-z1)) - 1.0f;
+              }
+              __nv_bfloat162 h = __floats2bfloat162_rn(z0, z1);
+              pk[e] = *reinterpret_cast<uint32_t *>(&h);
+            }
+            const int chunk = ((c0 & 63) >> 3) + j;
+            *reinterpret_cast<uint4 *>(box + ((chunk ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          }
+        } else {
+          const int b = m0 + r;
+          if (b < batch) {
+            double *yrow = Y + (size_t)b * ldy;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int n = n0 + c0 + j;
+              if (n < rows) {
+                // reduced-precision path: the activation is evaluated in fp32 (operands were bf16)
+                const float z = __uint_as_float(v[j]);
+                yrow[n] = (double)(act_kind == 0 ? __fdividef(2.0f, 1.0f + __expf(-z)) - 1.0f : z);
+              }
+            }
           }
         }
       }
+      if (OUT_BF16) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // staging writes visible to the TMA engine
+        epi_bar();
+        if (et == 0) {
+          tma_store_2d(&map_y, stage_out, n0, m0);  // out-of-range rows / columns are clipped by the tensor map
+          if (n0 + 64 < rows) tma_store_2d(&map_y, stage_out + BM * 128, n0 + 64, m0);
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
     }
+    if (OUT_BF16 && et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -267,26 +350,59 @@ int hpnn_dev_cast_bf16(const double *src, int ld_src, int rows, int cols, void *
   return 0;
 }
 
-// Wb: [rows x ldw] bf16, Xb: [batch x ldx] bf16 (ldw, ldx multiples of 8, base 16-byte aligned)
-int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y,
-                       int ldy, int act_kind, void *stream) {
-  if ((ldw % 8) || (ldx % 8) || ((uintptr_t)Wb & 15) || ((uintptr_t)Xb & 15)) {
+// Tensor maps are cached: encoding one costs a driver call, and an inference loop uses the same few
+// (pointer, shape) combinations over and over.
+struct MapKey {
+  const void *base;
+  int rows, cols, ld;
+  bool operator==(const MapKey &o) const { return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld; }
+};
+static const CUtensorMap *cached_map(const void *base, int rows, int cols, int ld) {
+  constexpr int kSlots = 64;
+  static MapKey keys[kSlots];
+  static CUtensorMap maps[kSlots];
+  static int used = 0, next = 0;
+  const MapKey k{base, rows, cols, ld};
+  for (int i = 0; i < used; ++i)
+    if (keys[i] == k) return &maps[i];
+  const int slot = used < kSlots ? used++ : (next++ % kSlots);
+  if (!umma::make_map(&maps[slot], base, rows, cols, ld, umma::BM)) return nullptr;
+  keys[slot] = k;
+  return &maps[slot];
+}
+
+static int launch_umma(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y, int ldy,
+                       void *Yb, int ldyb, int act_kind, void *stream) {
+  if ((ldw % 8) || (ldx % 8) || ((uintptr_t)Wb & 15) || ((uintptr_t)Xb & 15) || (Yb && ((ldyb % 8) || ((uintptr_t)Yb & 15)))) {
     set_error_msg("hpnn_dev_gemm_bf16: operands must be 16-byte aligned with leading dimensions % 8 == 0");
     return -1;
   }
-  CUtensorMap mx, mw;
-  if (!umma::make_map(&mx, Xb, batch, cols, ldx, umma::BM) || !umma::make_map(&mw, Wb, rows, cols, ldw, umma::BN)) {
+  const CUtensorMap *mx = cached_map(Xb, batch, cols, ldx), *mw = cached_map(Wb, rows, cols, ldw);
+  const CUtensorMap *my = Yb ? cached_map(Yb, batch, rows, ldyb) : mx;
+  if (!mx || !mw || !my) {
     set_error_msg("hpnn_dev_gemm_bf16: cuTensorMapEncodeTiled failed");
     return -1;
   }
-  cudaError_t e = cudaFuncSetAttribute(umma::k_gemm_bf16_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, umma::SMEM_BYTES);
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  const int ntiles = ((rows + umma::BN - 1) / umma::BN) * ((batch + umma::BM - 1) / umma::BM);
+  const int grid = ntiles < sms ? ntiles : sms;
+  const void *kfn = Yb ? (const void *)umma::k_gemm_bf16_umma<true> : (const void *)umma::k_gemm_bf16_umma<false>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, umma::SMEM_BYTES);
   if (e != cudaSuccess) {
     set_error("cudaFuncSetAttribute(k_gemm_bf16_umma)", e);
     return -1;
   }
-  dim3 grid((rows + umma::BN - 1) / umma::BN, (batch + umma::BM - 1) / umma::BM);
-  umma::k_gemm_bf16_umma<<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(mx, mw, batch, rows, cols, Y, ldy,
-                                                                                         act_kind);
+  if (Yb)
+    umma::k_gemm_bf16_umma<true><<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(*mx, *mw, *my, batch, rows,
+                                                                                               cols, nullptr, 0, act_kind);
+  else
+    umma::k_gemm_bf16_umma<false><<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(*mx, *mw, *my, batch, rows,
+                                                                                                cols, Y, ldy, act_kind);
   e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("k_gemm_bf16_umma", e);
@@ -294,6 +410,22 @@ int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *
   }
   ++g_launches;
   return 0;
+}
+
+// Wb: [rows x ldw] bf16, Xb: [batch x ldx] bf16 (ldw, ldx multiples of 8, base 16-byte aligned); FP64 result
+int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y,
+                       int ldy, int act_kind, void *stream) {
+  return launch_umma(Wb, ldw, rows, cols, Xb, ldx, batch, Y, ldy, nullptr, 0, act_kind, stream);
+}
+// same GEMM, bf16 result [batch x ldyb] for the next layer's GEMM (pad columns up to ldyb are NOT written:
+// zero the buffer once)
+int hpnn_dev_gemm_bf16_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, void *Yb,
+                            int ldyb, int act_kind, void *stream) {
+  if (!Yb) {
+    set_error_msg("hpnn_dev_gemm_bf16_bf16: null output");
+    return -1;
+  }
+  return launch_umma(Wb, ldw, rows, cols, Xb, ldx, batch, nullptr, 0, Yb, ldyb, act_kind, stream);
 }
 
 }  // extern "C"

@@ -204,6 +204,7 @@ class HpnnNet:
 
     def train_sample_async(self, opts: N.TrainOpts, slot: int = 0) -> None:
         """Enqueue the persistent trainer for the sample currently in the arena."""
+        self._w_bf16 = None  # the weights are about to change
         res_ptr = self._res_dev.data_ptr() + (slot % self._n_slots) * C.sizeof(N.TrainResult)
         N.check(self.lib.hpnn_dev_train_sample(C.byref(self.net), C.byref(opts), 0, res_ptr, self._stream()),
                 "hpnn_dev_train_sample")
@@ -260,6 +261,19 @@ class HpnnNet:
             raise RuntimeError("forward_batch on a row-split net: use parallel.tp.forward_batch_tp")
         H = X.to(self.device, torch.float64).contiguous()
         NL = self.n_layers
+        if precision == "bf16":
+            # tensor-core chain: bf16 weights are cast once and cached until the weights change; hidden
+            # layers hand bf16 activations from GEMM to GEMM, only the last layer produces FP64
+            if getattr(self, "_w_bf16", None) is None:
+                self._w_bf16 = [ops.cast_bf16(self.W_full[l], self.dims[l]) for l in range(NL)]
+            Hb = ops.cast_bf16(H, self.dims[0])
+            for l in range(NL - 1):
+                Hb = ops.gemm_bf16_chain(self._w_bf16[l], Hb, self.dims[l], 0)
+            kind = 1 if self.type == N.TYPE_SNN else 0
+            H = ops.gemm_bf16(self._w_bf16[NL - 1], Hb, self.dims[NL - 1], None, kind)
+            if self.type == N.TYPE_SNN:
+                ops.softmax_rows_(H, stable_softmax)
+            return H
         for l in range(NL):
             last = l == NL - 1
             kind = 1 if (last and self.type == N.TYPE_SNN) else 0
@@ -286,6 +300,7 @@ class HpnnNet:
         return Kernel(list(self.dims), ws, self.name)
 
     def load_weights(self, kernel: Kernel) -> None:
+        self._w_bf16 = None
         for l, W in enumerate(self.W_full):
             r0 = self.net.row0[l]
             src = torch.from_numpy(np.ascontiguousarray(kernel.weights[l][r0:r0 + self.net.rows[l]]))

@@ -147,6 +147,17 @@ def gemm_bf16(Wb: torch.Tensor, Xb: torch.Tensor, cols: int, Y: Optional[torch.T
     return Y
 
 
+def gemm_bf16_chain(Wb: torch.Tensor, Xb: torch.Tensor, cols: int, act_kind: int = 0) -> torch.Tensor:
+    """K-T for hidden layers: bf16 in, bf16 out ``[B, pad8(N)]`` (activation in fp32), written by TMA
+    stores -- the result is the next layer's GEMM operand, no FP64 round trip and no cast kernel."""
+    lib = N.load()
+    rows, B = Wb.shape[0], Xb.shape[0]
+    Yb = torch.zeros((B, (rows + 7) & ~7), dtype=torch.bfloat16, device=Wb.device)  # pad columns stay zero
+    N.check(lib.hpnn_dev_gemm_bf16_bf16(Wb.data_ptr(), Wb.stride(0), rows, cols, Xb.data_ptr(), Xb.stride(0), B,
+                                        Yb.data_ptr(), Yb.stride(0), act_kind, _s()), "hpnn_dev_gemm_bf16_bf16")
+    return Yb
+
+
 def softmax_rows_(Z: torch.Tensor, stable: bool = False) -> torch.Tensor:
     lib = N.load()
     B, n = Z.shape

@@ -317,6 +317,9 @@ int hpnn_dev_world_barrier(void *const *flags_all, int rank, int world, unsigned
 int hpnn_dev_cast_bf16(const double *src, int ld_src, int rows, int cols, void *dst_bf16, int ld_dst, void *stream);
 int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y,
                        int ldy, int act_kind, void *stream);
+/* same GEMM with a bf16 result [batch x ldyb] that feeds the next layer's GEMM directly (hidden layers) */
+int hpnn_dev_gemm_bf16_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, void *Yb,
+                            int ldyb, int act_kind, void *stream);
 /* row-wise softmax exp(z-1)/(TINY+sum) on a [batch x n] matrix (in place) */
 int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void *stream);
 

@@ -45,3 +45,26 @@ def test_forward_batch_bf16_close_to_fp64():
     torch.testing.assert_close(Y16, Y64, atol=5e-3, rtol=0)
     torch.testing.assert_close(Y64.sum(1), torch.ones(64, dtype=torch.float64, device="cuda"), atol=1e-9, rtol=0)
     net.close()
+
+
+@pytest.mark.parametrize("batch,rows,cols", [(128, 128, 64), (100, 70, 40), (333, 230, 851), (4096, 1000, 784),
+                                             (8192, 2048, 512)])
+@pytest.mark.parametrize("act_kind", [0, 1])
+def test_gemm_bf16_chain_output(batch, rows, cols, act_kind):
+    """bf16-in / bf16-out variant (hidden layers of the tensor-core chain): persistent tile loop, two TMEM
+    accumulators, swizzled staging + TMA store.  The largest shape gives every CTA about seven tiles."""
+    from hpnn_b200.ops import cuda as ops
+
+    W = _rand(rows, cols, seed=1) / np.sqrt(cols)
+    X = _rand(batch, cols, seed=2)
+    Wb, Xb = ops.cast_bf16(ops.padded_weights(W), cols), ops.cast_bf16(X, cols)
+    Yb = ops.gemm_bf16_chain(Wb, Xb, cols, act_kind)
+    assert Yb.dtype == torch.bfloat16 and Yb.shape == (batch, (rows + 7) & ~7)
+    ref = Xb[:, :cols].double() @ Wb[:, :cols].double().T
+    if act_kind == 0:
+        ref = R.act(ref)
+    torch.testing.assert_close(Yb[:, :rows].double(), ref, atol=1e-2, rtol=8e-3)  # bf16 output: 8 mantissa bits
+    assert (Yb[:, rows:] == 0).all()
+    # and twice in a row on the same buffers (cached tensor maps)
+    Yb2 = ops.gemm_bf16_chain(Wb, Xb, cols, act_kind)
+    assert torch.equal(Yb, Yb2)
