@@ -28,14 +28,15 @@ void set_error_msg(const char *what);
 
 namespace umma {
 
-constexpr int BM = 128, BN = 128, BK = 64;       // tile (BK bf16 = one 128-byte swizzle row)
+constexpr int BM = 128, BN = 256, BK = 64;       // tile (BK bf16 = one 128-byte swizzle row); N = 256 halves the
+                                                 // shared-memory bytes per flop (A is read once per 256 columns)
 constexpr int UMMA_K = 16;                       // bf16 MMA depth
-constexpr int STAGES = 5;                        // 5 x 32 KB ring, one persistent CTA per SM
+constexpr int STAGES = 3;                        // 3 x 48 KB ring, one persistent CTA per SM
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;   // 32 KB
-constexpr int TMEM_COLS = 256;                   // two 128-column fp32 accumulators
+constexpr int TMEM_COLS = 2 * BN;                // two fp32 accumulators of BN columns: the whole TMEM
 constexpr int THREADS = 192;
-constexpr int OUT_BYTES = BM * BN * 2;           // bf16 output tile staged for the TMA store (32 KB)
+constexpr int OUT_BYTES = BM * BN * 2;           // bf16 output tile staged for the TMA store (64 KB)
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -270,8 +271,8 @@ __global__ void __launch_bounds__(THREADS, 1)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // staging writes visible to the TMA engine
         epi_bar();
         if (et == 0) {
-          tma_store_2d(&map_y, stage_out, n0, m0);  // out-of-range rows / columns are clipped by the tensor map
-          if (n0 + 64 < rows) tma_store_2d(&map_y, stage_out + BM * 128, n0 + 64, m0);
+          for (int bx = 0; bx < BN / 64; ++bx)  // out-of-range rows / columns are clipped by the tensor map
+            if (n0 + 64 * bx < rows) tma_store_2d(&map_y, stage_out + bx * (BM * 128), n0 + 64 * bx, m0);
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
@@ -354,19 +355,21 @@ int hpnn_dev_cast_bf16(const double *src, int ld_src, int rows, int cols, void *
 // (pointer, shape) combinations over and over.
 struct MapKey {
   const void *base;
-  int rows, cols, ld;
-  bool operator==(const MapKey &o) const { return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld; }
+  int rows, cols, ld, box;
+  bool operator==(const MapKey &o) const {
+    return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box == o.box;
+  }
 };
-static const CUtensorMap *cached_map(const void *base, int rows, int cols, int ld) {
+static const CUtensorMap *cached_map(const void *base, int rows, int cols, int ld, int box_rows) {
   constexpr int kSlots = 64;
   static MapKey keys[kSlots];
   static CUtensorMap maps[kSlots];
   static int used = 0, next = 0;
-  const MapKey k{base, rows, cols, ld};
+  const MapKey k{base, rows, cols, ld, box_rows};
   for (int i = 0; i < used; ++i)
     if (keys[i] == k) return &maps[i];
   const int slot = used < kSlots ? used++ : (next++ % kSlots);
-  if (!umma::make_map(&maps[slot], base, rows, cols, ld, umma::BM)) return nullptr;
+  if (!umma::make_map(&maps[slot], base, rows, cols, ld, box_rows)) return nullptr;
   keys[slot] = k;
   return &maps[slot];
 }
@@ -377,8 +380,8 @@ static int launch_umma(const void *Wb, int ldw, int rows, int cols, const void *
     set_error_msg("hpnn_dev_gemm_bf16: operands must be 16-byte aligned with leading dimensions % 8 == 0");
     return -1;
   }
-  const CUtensorMap *mx = cached_map(Xb, batch, cols, ldx), *mw = cached_map(Wb, rows, cols, ldw);
-  const CUtensorMap *my = Yb ? cached_map(Yb, batch, rows, ldyb) : mx;
+  const CUtensorMap *mx = cached_map(Xb, batch, cols, ldx, umma::BM), *mw = cached_map(Wb, rows, cols, ldw, umma::BN);
+  const CUtensorMap *my = Yb ? cached_map(Yb, batch, rows, ldyb, umma::BM) : mx;
   if (!mx || !mw || !my) {
     set_error_msg("hpnn_dev_gemm_bf16: cuTensorMapEncodeTiled failed");
     return -1;
