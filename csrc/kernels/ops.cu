@@ -129,7 +129,15 @@ __device__ __forceinline__ void dmma_m8n8k4(double (&c)[2], double a, double b) 
 struct GemmDst {
   double *y[HPNN_MAX_WORLD];
   int n, col0;
+  double *y_mc;  // the same matrix at the NVLS multicast address (one store reaches every rank), or nullptr
 };
+// two adjacent doubles through the multicast mapping in one 16-byte store (bits travel as 4 x b32)
+__device__ __forceinline__ void multimem_st_2f64(double *mc, double a, double b) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc),
+               "f"(__uint_as_float((unsigned)__double2loint(a))), "f"(__uint_as_float((unsigned)__double2hiint(a))),
+               "f"(__uint_as_float((unsigned)__double2loint(b))), "f"(__uint_as_float((unsigned)__double2hiint(b)))
+               : "memory");
+}
 __global__ void __launch_bounds__(128)
     k_forward_batch_f64(const double *__restrict__ W, int ld, int rows, int cols, const double *__restrict__ X,
                         int ldx, int batch, GemmDst dst, int ldy, int act_kind) {
@@ -192,15 +200,24 @@ __global__ void __launch_bounds__(128)
     const int b = b0 + wm + 8 * i + g;
     if (b >= batch) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int r = r0 + wn + 8 * j + 2 * q + e;
-        if (r < rows) {
-          const double y = act_kind == 0 ? act_f(acc[i][j][e]) : acc[i][j][e];
-          for (int p = 0; p < dst.n; ++p) dst.y[p][(size_t)b * ldy + dst.col0 + r] = y;
+    for (int j = 0; j < 4; ++j) {
+      const int r = r0 + wn + 8 * j + 2 * q;
+      const double y0 = act_kind == 0 ? act_f(acc[i][j][0]) : acc[i][j][0];
+      const double y1 = act_kind == 0 ? act_f(acc[i][j][1]) : acc[i][j][1];
+      const size_t o = (size_t)b * ldy + dst.col0 + r;
+      if (dst.y_mc) {  // GEMM fused with the all-gather of its output: the switch replicates the store
+        if (r + 1 < rows && !(o & 1)) multimem_st_2f64(dst.y_mc + o, y0, y1);
+        else {
+          if (r < rows) multimem_st_f64(dst.y_mc + o, y0);
+          if (r + 1 < rows) multimem_st_f64(dst.y_mc + o + 1, y1);
+        }
+      } else {
+        for (int p = 0; p < dst.n; ++p) {
+          if (r < rows) dst.y[p][o] = y0;
+          if (r + 1 < rows) dst.y[p][o + 1] = y1;
         }
       }
+    }
   }
 }
 
@@ -378,6 +395,7 @@ int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, cons
   GemmDst dst;
   dst.n = 1;
   dst.col0 = 0;
+  dst.y_mc = nullptr;
   dst.y[0] = Y;
   k_forward_batch_f64<<<grid, 128, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, dst, ldy, act_kind);
   HPNN_CHECK_LAUNCH("k_forward_batch_f64");
@@ -389,6 +407,13 @@ int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, cons
 // with the all-gather of its result over NVLink peer memory).
 int hpnn_dev_forward_batch_f64_tp(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
                                   double *const *Y_all, int n_ranks, int col0, int ldy, int act_kind, void *stream) {
+  return hpnn_dev_forward_batch_f64_tp_mc(W, ld, rows, cols, X, ldx, batch, Y_all, nullptr, n_ranks, col0, ldy, act_kind, stream);
+}
+// Y_mc != NULL: the activation matrices are one symmetric allocation with an NVLS multicast mapping; the
+// epilogue then issues ONE 16-byte multimem.st per pair of results instead of a store per rank
+int hpnn_dev_forward_batch_f64_tp_mc(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
+                                     double *const *Y_all, double *Y_mc, int n_ranks, int col0, int ldy, int act_kind,
+                                     void *stream) {
   if ((ld & 1) || (ldx & 1) || ((uintptr_t)W & 15) || ((uintptr_t)X & 15) || n_ranks < 1 || n_ranks > HPNN_MAX_WORLD) {
     set_error_msg("hpnn_dev_forward_batch_f64_tp: bad arguments");
     return -1;
@@ -397,6 +422,7 @@ int hpnn_dev_forward_batch_f64_tp(const double *W, int ld, int rows, int cols, c
   GemmDst dst;
   dst.n = n_ranks;
   dst.col0 = col0;
+  dst.y_mc = Y_mc;
   for (int p = 0; p < HPNN_MAX_WORLD; ++p) dst.y[p] = p < n_ranks ? Y_all[p] : nullptr;
   dim3 grid((rows + GB - 1) / GB, (batch + GB - 1) / GB);
   k_forward_batch_f64<<<grid, 128, 0, (cudaStream_t)stream>>>(W, ld, rows, cols, X, ldx, batch, dst, ldy, act_kind);
@@ -415,7 +441,15 @@ __global__ void k_world_barrier_v(FlagPtrs f, int rank, int world, unsigned long
   __syncthreads();
   if ((int)threadIdx.x < world && (int)threadIdx.x != rank) {
     st_relaxed_sys(f.p[threadIdx.x] + rank, epoch);
+    // bounded: a peer that never arrives must not hang this GPU (10 s, then the barrier is given up)
+    unsigned long long t0 = 0, now;
+    unsigned spins = 0;
     while (ld_relaxed_sys(f.p[rank] + threadIdx.x) < epoch) {
+      if ((++spins & 1023u) == 0) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (!t0) t0 = now;
+        else if (now - t0 > 10000000000ull) break;
+      }
     }
   }
   __syncthreads();

@@ -126,6 +126,7 @@ def _declare(lib):
         "hpnn_dev_forward_batch_f64": (i, [vp, i, i, i, vp, i, i, vp, i, i, vp]),
         "hpnn_dev_softmax_rows": (i, [vp, i, i, i, i, vp]),
         "hpnn_dev_forward_batch_f64_tp": (i, [vp, i, i, i, vp, i, i, C.POINTER(vp), i, i, i, i, vp]),
+        "hpnn_dev_forward_batch_f64_tp_mc": (i, [vp, i, i, i, vp, i, i, C.POINTER(vp), vp, i, i, i, i, vp]),
         "hpnn_dev_world_barrier": (i, [C.POINTER(vp), i, i, C.c_ulonglong, vp]),
         "hpnn_dev_grad_merge": (i, [vp, ll, C.POINTER(vp), i, d, vp]),
         "hpnn_dev_launch_count": (ll, [i]),

@@ -57,9 +57,10 @@ class TPBatchRunner:
             off = (l & 1) * self.act_doubles
             Yfull = self.buf.local[off: off + B * ldy].view(B, ldy)
             if mode == "fused":
-                N.check(self.lib.hpnn_dev_forward_batch_f64_tp(
+                mc = (self.buf.mc_ptr + 8 * off) if self.buf.mc_ptr else None  # NVLS: one store reaches every rank
+                N.check(self.lib.hpnn_dev_forward_batch_f64_tp_mc(
                     net.W_full[l].data_ptr() if rows else None, net.net.ld[l], rows, net.dims[l], H.data_ptr(), H.stride(0), B,
-                    self._ptrs(off), net.world, r0, ldy, kind, stream), "hpnn_dev_forward_batch_f64_tp")
+                    self._ptrs(off), mc, net.world, r0, ldy, kind, stream), "hpnn_dev_forward_batch_f64_tp_mc")
                 self.epoch += 1
                 N.check(self.lib.hpnn_dev_world_barrier(flags, net.rank, net.world, self.epoch, stream),
                         "hpnn_dev_world_barrier")

@@ -309,6 +309,11 @@ int hpnn_dev_forward_batch_f64(const double *W, int ld, int rows, int cols, cons
  * are rank p's buffers as mapped into this process; epoch must grow by one per call. */
 int hpnn_dev_forward_batch_f64_tp(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
                                   double *const *Y_all, int n_ranks, int col0, int ldy, int act_kind, void *stream);
+/* same with the all-gather through the NVLS multicast mapping of the activation matrices (Y_mc from
+ * hpnn_symm_mc_ptr, NULL = peer stores): one 16-byte multimem.st per pair of results */
+int hpnn_dev_forward_batch_f64_tp_mc(const double *W, int ld, int rows, int cols, const double *X, int ldx, int batch,
+                                     double *const *Y_all, double *Y_mc, int n_ranks, int col0, int ldy, int act_kind,
+                                     void *stream);
 int hpnn_dev_world_barrier(void *const *flags_all, int rank, int world, unsigned long long epoch, void *stream);
 /* opt-in reduced precision (K-T): bf16 operands, fp32 accumulation on the tcgen05 tensor cores
  * (TMA -> shared memory -> tcgen05.mma -> TMEM -> epilogue), FP64 result.  Never used for parity.
