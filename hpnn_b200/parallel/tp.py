@@ -10,6 +10,7 @@
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -57,7 +58,11 @@ class TPBatchRunner:
             off = (l & 1) * self.act_doubles
             Yfull = self.buf.local[off: off + B * ldy].view(B, ldy)
             if mode == "fused":
-                mc = (self.buf.mc_ptr + 8 * off) if self.buf.mc_ptr else None  # NVLS: one store reaches every rank
+                # NVLS: one store reaches every rank.  At 2 ranks two plain stores (one local, one peer) are
+                # faster than a trip through the switch (8.3 M vs 7.1 M samples/s at batch 4096), so the
+                # multicast epilogue is used from 4 ranks on (HPNN_TP_BATCH_MC=0/1 overrides)
+                use_mc = os.environ.get("HPNN_TP_BATCH_MC", "1" if net.world >= 4 else "0") == "1"
+                mc = (self.buf.mc_ptr + 8 * off) if (self.buf.mc_ptr and use_mc) else None
                 N.check(self.lib.hpnn_dev_forward_batch_f64_tp_mc(
                     net.W_full[l].data_ptr() if rows else None, net.net.ld[l], rows, net.dims[l], H.data_ptr(), H.stride(0), B,
                     self._ptrs(off), mc, net.world, r0, ldy, kind, stream), "hpnn_dev_forward_batch_f64_tp_mc")
