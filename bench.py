@@ -39,6 +39,8 @@ sys.path.insert(0, ROOT)
 CONFIGS = {
     "wide_ann": ("ANN", "BP", 784, [8192, 8192, 8192, 8192], 10,
                  "Wide ANN 8192x4 hidden layers BP, row split (BASELINE.json config 4)"),
+    "wide_ann_bpm": ("ANN", "BPM", 784, [8192, 8192, 8192, 8192], 10,
+                     "Wide ANN 8192x4 hidden layers, momentum (BPM) variant of BASELINE.json config 4"),
     "snn_mnist": ("SNN", "BPM", 784, [1000, 1000], 10,
                   "SNN 784-1000-1000-10 BPM online training (BASELINE.json config 2)"),
     "xrd_snn": ("SNN", "BPM", 851, [230], 230,
