@@ -18,6 +18,8 @@
 #include "libhpnn.h"
 #include "libhpnn/ann.h"
 #include "libhpnn/snn.h"
+#include "libhpnn/cuda_ann.h"
+#include "libhpnn/cuda_snn.h"
 
 extern "C" {
 nn_runtime lib_runtime;  // one runtime per process, as in the reference (src/libhpnn.c:60)
@@ -952,6 +954,74 @@ DOUBLE snn_train_BP(kernel_ann *kernel, DOUBLE *in, DOUBLE *out, DOUBLE delta) {
 }
 DOUBLE snn_train_BPM(kernel_ann *kernel, DOUBLE *in, DOUBLE *out, DOUBLE alpha, DOUBLE delta) {
   return kernel ? train_sample(kernel, HPNN_TYPE_SNN, HPNN_TRAIN_BPM, in, out, alpha, delta) : 0.;
+}
+
+/* ==================== device layer: cuda_ann.h / cuda_snn.h ==================== */
+// The reference's scuda_* functions (src/cuda_ann.cu:192-4103, src/cuda_snn.cu) operate on device
+// pointers kept inside kernel_ann.  Here the device copy lives behind the kernel (Shim::dev), so these
+// entry points are the same operations phrased on the host mirror; `cudas` is accepted and ignored.
+static layer_ann *layer_at(kernel_ann *k, int index) {
+  if (!k || index < 0) return nullptr;
+  return (UINT)index < k->n_hiddens ? &k->hiddens[index] : &k->output;
+}
+int64_t scuda_ann_allocate(kernel_ann *kernel, cudastreams *) {
+  Shim *s = as_shim(kernel);
+  if (!s || !s->host) return 0;
+  hpnn_net *dev = device_for(s, HPNN_TYPE_ANN, s->dev_momentum);
+  return dev ? (int64_t)hpnn_net_device_bytes(dev) : 0;
+}
+void scuda_ann_deallocate(kernel_ann *kernel, cudastreams *) {
+  Shim *s = as_shim(kernel);
+  if (!s) return;
+  sync_to_host(s);
+  drop_device(s);
+}
+int64_t scuda_ann_allocate_momentum(kernel_ann *kernel, cudastreams *) {
+  Shim *s = as_shim(kernel);
+  if (!s || !s->host) return 0;
+  ann_momentum_init(kernel);
+  int64_t bytes = 0;
+  for (int l = 0; l < hpnn_kernel_n_layers(s->host); ++l)
+    bytes += (int64_t)sizeof(double) * hpnn_kernel_dim(s->host, l) * hpnn_kernel_dim(s->host, l + 1);
+  return bytes;
+}
+BOOL scuda_ann_free_momentum(kernel_ann *kernel, cudastreams *) {
+  if (!as_shim(kernel)) return FALSE;
+  ann_momentum_free(kernel);
+  return TRUE;
+}
+void scuda_ann_weight_transfer_C2G(kernel_ann *kernel, int index, DOUBLE *weight, cudastreams *) {
+  Shim *s = as_shim(kernel);
+  layer_ann *L = layer_at(kernel, index);
+  if (!s || !s->host || !L || !weight) return;
+  sync_to_host(s);
+  memcpy(L->weights, weight, sizeof(double) * (size_t)L->n_neurons * L->n_inputs);
+  if (s->dev) s->dev_stale = true;  // re-uploaded before the next device step
+}
+void scuda_ann_weight_transfer_G2C(kernel_ann *kernel, int index, DOUBLE **weight, cudastreams *) {
+  Shim *s = as_shim(kernel);
+  layer_ann *L = layer_at(kernel, index);
+  if (!s || !s->host || !L || !weight || !*weight) return;
+  sync_to_host(s);
+  memcpy(*weight, L->weights, sizeof(double) * (size_t)L->n_neurons * L->n_inputs);
+}
+void scuda_ann_forward(kernel_ann *kernel, cudastreams *) { ann_kernel_run(kernel); }
+void scuda_snn_forward(kernel_ann *kernel, cudastreams *) { snn_kernel_run(kernel); }
+static double device_layer_error(kernel_ann *kernel, int type, const double *train) {
+  Shim *s = as_shim(kernel);
+  if (!s || !s->host || !train) return 0.;
+  return hpnn_cpu_error(s->host, type, train);  // from the output vector the last forward left in the mirror
+}
+double scuda_ann_error(kernel_ann *kernel, double *train, cudastreams *) { return device_layer_error(kernel, HPNN_TYPE_ANN, train); }
+double scuda_snn_error(kernel_ann *kernel, double *train, cudastreams *) { return device_layer_error(kernel, HPNN_TYPE_SNN, train); }
+double scuda_ann_train(kernel_ann *kernel, double *train, cudastreams *) { return ann_kernel_train(kernel, train); }
+double scuda_snn_train(kernel_ann *kernel, double *train, cudastreams *) { return snn_kernel_train(kernel, train); }
+void scuda_ann_raz_momentum(kernel_ann *kernel, cudastreams *) { ann_raz_momentum(kernel); }
+double scuda_ann_train_momentum(kernel_ann *kernel, double *train, double moment, cudastreams *) {
+  return ann_kernel_train_momentum(kernel, train, moment);
+}
+double scuda_snn_train_momentum(kernel_ann *kernel, double *train, double moment, cudastreams *) {
+  return snn_kernel_train_momentum(kernel, train, moment);
 }
 
 }  // extern "C"

@@ -360,3 +360,57 @@ def test_c_driver_under_a_multi_process_launcher(artefacts, tmp_path):
     # the driver opens kernel.opt on every rank (so does the reference's), only rank 0 writes into it
     assert (dirs[0] / "kernel.opt").stat().st_size > 0
     assert all(not (dirs[r] / "kernel.opt").exists() or (dirs[r] / "kernel.opt").stat().st_size == 0 for r in (1, 2))
+
+
+DEVICE_LAYER_C = r"""
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <libhpnn.h>
+#include <libhpnn/cuda_snn.h>
+/* the reference's device-layer entry points (include/libhpnn/cuda_ann.h:40-52, cuda_snn.h:33-39) */
+int main(void){
+    UINT hid[2]={5,4}, seed=77;
+    DOUBLE in[8]={.1,.2,.3,.4,.5,.6,.7,.8}, t[3]={1.,-1.,-1.};
+    nn_init_all(0);
+    kernel_ann *k=ann_generate(&seed,8,2,3,hid);
+    if(!k) return 1;
+    scuda_ann_allocate(k,NULL);
+    DOUBLE *w=(DOUBLE*)malloc(sizeof(DOUBLE)*5*8), *back=(DOUBLE*)malloc(sizeof(DOUBLE)*5*8);
+    for(int i=0;i<40;i++) w[i]=0.01*(i%9)-0.03;
+    scuda_ann_weight_transfer_C2G(k,0,w,NULL);
+    scuda_ann_weight_transfer_G2C(k,0,&back,NULL);
+    if(memcmp(w,back,sizeof(DOUBLE)*40)) return 2;
+    memcpy(k->in,in,sizeof(in));
+    scuda_ann_forward(k,NULL);
+    double e0=scuda_ann_error(k,t,NULL);
+    double d=scuda_ann_train(k,t,NULL);            /* one BP iteration: returns Ep - Epr */
+    double e1=scuda_ann_error(k,t,NULL);
+    printf("E0=%.12f dE=%.6e E1=%.12f\n",e0,d,e1);
+    if(!(e0>0.) || !(d>0.) || fabs((e0-e1)-d)>1e-12) return 3;
+    if(scuda_ann_allocate_momentum(k,NULL)<=0) return 4;
+    scuda_ann_raz_momentum(k,NULL);
+    if(!(scuda_ann_train_momentum(k,t,0.2,NULL)>0.)) return 5;
+    if(scuda_ann_free_momentum(k,NULL)!=TRUE) return 6;
+    scuda_snn_forward(k,NULL);
+    double s=0.; for(UINT i=0;i<k->n_outputs;i++) s+=k->output.vec[i];
+    if(fabs(s-1.)>1e-9) return 7;                   /* a soft-max came out */
+    if(!(scuda_snn_error(k,t,NULL)==scuda_snn_error(k,t,NULL))) return 8;
+    scuda_ann_deallocate(k,NULL);
+    printf("DEVICE_LAYER_OK\n");
+    return 0;
+}
+"""
+
+
+def test_device_layer_entry_points(artefacts, tmp_path):
+    """scuda_ann_* / scuda_snn_* exist with the reference's signatures and host-mirror semantics."""
+    src = tmp_path / "device_layer.c"
+    src.write_text(DEVICE_LAYER_C)
+    exe = tmp_path / "device_layer"
+    r = subprocess.run(["gcc", "-O1", f"-I{ROOT}/include", str(src), "-o", str(exe), f"-L{LIBDIR}", "-lhpnn",
+                        f"-Wl,-rpath,{LIBDIR}", "-lm"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = _run([str(exe)], tmp_path)
+    assert r.returncode == 0 and "DEVICE_LAYER_OK" in r.stdout, (r.returncode, r.stdout, r.stderr)
