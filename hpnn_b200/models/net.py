@@ -40,9 +40,17 @@ def split_rows(n: int, rank: int, world: int):
     return r0, (rank + 1) * n // world - r0
 
 
-class HpnnNet:
+class HpnnNet(torch.nn.Module):
+    """``torch.nn.Module`` whose parameters are this rank's padded weight rows (``requires_grad=False``:
+    training is the library's own BP / BPM, not autograd) and whose buffers are the momenta, so
+    ``parameters()``, ``state_dict()`` / ``load_state_dict()`` and ``forward(X)`` work as usual.  The
+    kernels hold raw pointers into these tensors: ``.to()`` / ``.double()`` that keep device and dtype
+    are fine (pointers are refreshed), anything else is refused.  (``net.type`` is the network type
+    ANN / SNN as in the reference's ``nn_def``; it shadows ``Module.type()``.)"""
+
     def __init__(self, kernel: Kernel, nn_type: int, device: Optional[torch.device] = None,
                  momentum: bool = True, group=None, virtual_rank: Optional[tuple] = None):
+        super().__init__()
         if not torch.cuda.is_available():
             raise RuntimeError("HpnnNet needs a CUDA device (use the 'cpu' or 'torch' engine otherwise)")
         self.lib = N.load()
@@ -77,21 +85,20 @@ class HpnnNet:
             raise ValueError("invalid network layout")
         self.net = net
         # ---- weights (+ momentum): private, padded leading dimension, owned rows only
-        self.W_full: List[torch.Tensor] = []
-        self.dW_full: List[Optional[torch.Tensor]] = []
+        self._W = torch.nn.ParameterList()
+        self._has_momentum = bool(momentum)
         for l in range(NL):
             Wl = torch.zeros((net.rows[l], net.ld[l]), dtype=torch.float64, device=self.device)
             r0 = net.row0[l]
             src = torch.from_numpy(np.ascontiguousarray(kernel.weights[l][r0:r0 + net.rows[l]]))
             Wl[:, : self.dims[l]].copy_(src)
-            self.W_full.append(Wl)
+            self._W.append(torch.nn.Parameter(Wl, requires_grad=False))
             net.W[l] = Wl.data_ptr() if Wl.numel() else None
             if momentum:
                 Ml = torch.zeros_like(Wl)
-                self.dW_full.append(Ml)
+                self.register_buffer(f"momentum_{l}", Ml)
                 net.dW[l] = Ml.data_ptr() if Ml.numel() else None
             else:
-                self.dW_full.append(None)
                 net.dW[l] = None
         # ---- symmetric arena + private sync words.  Several ranks: the arena is a SymmetricBuffer
         # (VMM allocation mapped into every process, NVLS multicast address when the fabric has one;
@@ -150,6 +157,33 @@ class HpnnNet:
                 self.close()
         except Exception:
             pass
+
+    # ------------------------------------------------------------------ nn.Module plumbing
+    @property
+    def W_full(self) -> List[torch.Tensor]:
+        """Owned rows of every layer in their padded storage ``[rows_l, ld_l]``."""
+        return [p.data for p in self._W]
+
+    @property
+    def dW_full(self) -> List[Optional[torch.Tensor]]:
+        return [getattr(self, f"momentum_{l}") if self._has_momentum else None for l in range(self.n_layers)]
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        for l, W in enumerate(self.W_full):  # the kernels address these tensors by pointer
+            if W.device != self.device or W.dtype != torch.float64:
+                raise RuntimeError("HpnnNet lives on %s in float64; build a new net for another device / dtype" % self.device)
+            self.net.W[l] = W.data_ptr() if W.numel() else None
+            M = self.dW_full[l]
+            self.net.dW[l] = M.data_ptr() if (M is not None and M.numel()) else None
+        self._w_bf16 = None
+        return out
+
+    def forward(self, X: torch.Tensor) -> torch.Tensor:
+        """``[B, n_in] -> [B, n_out]`` (batched FP64 path) or ``[n_in] -> [n_out]`` (persistent kernel)."""
+        if X.dim() == 2:
+            return self.forward_batch(X)
+        return self.run(X).clone()
 
     # ------------------------------------------------------------------ views
     @property

@@ -197,3 +197,29 @@ def test_row_panel_momentum_trainer_matches_cpu_engine(nn_type):
     finally:
         lib.hpnn_dev_set_lazy(-1, -1)
         lib.hpnn_dev_set_lazy_panel(-1)
+
+
+def test_hpnn_net_is_a_torch_module():
+    """parameters(), state_dict() / load_state_dict() and forward() of the device-resident net."""
+    from hpnn_b200.models.net import HpnnNet
+
+    k, _ = hp.generate_kernel(7, 20, [16, 12], 4)
+    k2, _ = hp.generate_kernel(8, 20, [16, 12], 4)
+    a, b = HpnnNet(k, N.TYPE_SNN), HpnnNet(k2, N.TYPE_SNN)
+    assert isinstance(a, torch.nn.Module)
+    ps = list(a.parameters())
+    assert len(ps) == 3 and not any(p.requires_grad for p in ps) and ps[0].shape == (16, 24)  # padded to 8 columns
+    assert sum(1 for _ in a.buffers()) == 3  # momenta
+    x = torch.rand(20, dtype=torch.float64, device="cuda")
+    X = torch.rand(5, 20, dtype=torch.float64, device="cuda")
+    ya = a(x)
+    assert not torch.allclose(ya, b(x))
+    b.load_state_dict(a.state_dict())  # copies in place: the kernels' pointers stay valid
+    torch.testing.assert_close(b(x), ya, atol=0, rtol=0)
+    torch.testing.assert_close(a(X)[0], a(X[0]), atol=1e-13, rtol=0)
+    a.double().to("cuda")  # same device and dtype: allowed, pointers refreshed
+    torch.testing.assert_close(a(x), ya, atol=0, rtol=0)
+    with pytest.raises(RuntimeError):
+        a.float()
+    a.close()
+    b.close()
