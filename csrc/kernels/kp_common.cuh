@@ -26,6 +26,7 @@ struct KP {
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
   int keep_l2;   // K-PL1: a rank's share of a layer fits L2, so the passes use caching loads instead of evict-first ones
+  int slicewise;  // K-PL1, several ranks, short panels: forward passes consume the peers' activations slice by slice
   int fold_out;  // K-PL1: the output layer is folded into the phases of the layer below (see train_lazy1.cu)
   int fault;  // fault injection (tests): 1 = this rank leaves at kernel entry, as if its launch had failed
   unsigned long long spin_budget_ns;  // longest time any wait may take before the job is abandoned (0 = unbounded)
@@ -54,6 +55,7 @@ struct WatchState {
   unsigned exit_now;  // CTA-uniform copy, written by thread 0 once per iteration
 };
 static __shared__ WatchState s_watch;
+static __shared__ unsigned s_kx;  // cross-rank barrier index of the last arrive (for Barrier::wait_rank)
 
 __device__ __forceinline__ unsigned long long global_ns() {
   unsigned long long t;
@@ -158,6 +160,57 @@ struct Barrier {
     }
     __syncthreads();
   }
+  // CTA 0, after its fence.sys: this rank's flag word (= kx) and +1 on the barrier counter, on every rank
+  __device__ __forceinline__ void signal(const hpnn_dev_net &n) {
+    if (n.arena_mc) {
+      unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags);
+      multimem_st_u64(f + n.rank, (unsigned long long)kx);
+      multimem_red_add_u64(f + kCounterSlot, 1ull);
+    } else {
+      for (int q = 0; q < n.world; ++q) {
+        unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags);
+        st_relaxed_sys(f + n.rank, (unsigned long long)kx);
+        red_add_relaxed_sys_u64(f + kCounterSlot, 1ull);
+      }
+    }
+  }
+  // Split barrier, arrive half (several ranks only): everything of sync_all except the wait for the other
+  // ranks.  The phase that follows consumes the peers' data slice by slice and waits per producer rank
+  // (wait_rank) right before it needs that rank's slice, so the NVLink flight and the other ranks' skew
+  // hide behind the weight stream.  Every CTA must wait for ALL ranks (its own included) before it
+  // arrives at the next barrier: that keeps the three rotating local counters safe.
+  __device__ __forceinline__ void arrive_all(const hpnn_dev_net &n) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned *c = sync + 32 * (k % 3u);
+      unsigned *prev = sync + 32 * ((k + 2u) % 3u);
+      ++k;
+      ++kx;
+      s_kx = kx;
+      red_add_release_gpu(c, 1u);
+      if (bid == 0) {
+        Spin sp;
+        while (ld_relaxed_gpu(c) != grid) {
+          if (sp.give_up()) break;
+        }
+        *prev = 0;
+        fence_sys();
+        signal(n);
+      }
+    }
+    __syncthreads();
+  }
+  // wait half: rank q's data of the last arrive_all is complete and visible (call from ONE lane per warp,
+  // __syncwarp afterwards)
+  __device__ __forceinline__ void wait_rank(const hpnn_dev_net &n, int q) const {
+    const unsigned long long want = (unsigned long long)s_kx;
+    const unsigned long long *f = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags) + q;
+    Spin sp;
+    while (ld_relaxed_sys(f) < want) {
+      if (sp.give_up()) return;
+    }
+    if (ld_acquire_sys(f) < want) s_watch.tripped = 1;
+  }
   __device__ __forceinline__ void finish() {  // call once, after the last barrier
     if (bid == 0 && threadIdx.x == 0) {
       sync[128] = k;
@@ -201,12 +254,7 @@ struct Barrier {
           }
           *prev = 0;
           fence_sys();  // release: everything this rank wrote is visible before the counter moves
-          if (n.arena_mc) {
-            multimem_red_add_u64(reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags) + kCounterSlot, 1ull);
-          } else {
-            for (int q = 0; q < n.world; ++q)
-              red_add_relaxed_sys_u64(reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags) + kCounterSlot, 1ull);
-          }
+          signal(n);
         }
         const unsigned long long *ctr = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags) + kCounterSlot;
         while (ld_relaxed_sys(ctr) < want) {

@@ -384,6 +384,67 @@ __device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, cons
   }
 }
 
+// z partials of a SHORT panel (<= 8 rows: 8 ranks on the wide shape) when the input vector is still arriving
+// from the other ranks: the row sums stay in registers across the whole row, the columns are walked in
+// chunks of 1024 starting with the chunk this rank produced itself, the weights of the next chunk are
+// already in flight while a warp waits (Barrier::wait_rank) for the ranks that own the columns of the
+// current one.  The weight stream never waits for NVLink; only the FMAs do.  x is read from the arena
+// (L2), two values per thread and chunk: no staging pass, no CTA-wide barrier until the panel is done.
+__device__ __forceinline__ void panel_z_chunks(const double *W, int ld, Panel pn, const double *x, const hpnn_dev_net &n,
+                                               int l, const Barrier &bar, double *zpart) {
+  constexpr int R = 8;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double2 zero2 = make_double2(0.0, 0.0);
+  const int nch = (ld + kPanelCols - 1) / kPanelCols;
+  const int ncols = n.dims[l];  // real columns = rows of layer l-1, split over the ranks
+  int own0 = 0;
+  for (int q = 0; q < n.rank; ++q) own0 += s_rows_of[l - 1][q];
+  const int c_first = min(own0 / kPanelCols, nch - 1);
+  double acc[R];
+#pragma unroll
+  for (int i = 0; i < R; ++i) acc[i] = 0.0;
+  double2 wa[R], wb[R];
+  auto loadw = [&](double2 (&w)[R], int cc) {
+    const int c = (c_first + cc) % nch;
+    const int col = c * kPanelCols + 2 * threadIdx.x;
+    const bool on = cc < nch && col < ld;
+#pragma unroll
+    for (int i = 0; i < R; ++i)
+      w[i] = (on && i < pn.cnt) ? ldw2<false>(reinterpret_cast<const double2 *>(W + (size_t)(pn.r0 + i) * ld + col)) : zero2;
+  };
+  auto consume = [&](double2 (&w)[R], int cc) {
+    if (cc >= nch) return;
+    const int c = (c_first + cc) % nch;
+    const int lo = c * kPanelCols, hi = min(ncols, lo + kPanelCols);
+    if (lane == 0) {  // the ranks that produced columns [lo, hi)
+      int r0 = 0;
+      for (int q = 0; q < n.world; ++q) {
+        const int r1 = r0 + s_rows_of[l - 1][q];
+        if (r0 < hi && r1 > lo) bar.wait_rank(n, q);
+        r0 = r1;
+      }
+    }
+    __syncwarp();
+    const int col = lo + 2 * threadIdx.x;
+    const double2 x2 = col < ld ? ldg_cg2(reinterpret_cast<const double2 *>(x + col)) : zero2;
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      acc[i] = fma(w[i].x, x2.x, acc[i]);
+      acc[i] = fma(w[i].y, x2.y, acc[i]);
+    }
+  };
+  loadw(wa, 0);
+  for (int cc = 0; cc < nch; cc += 2) {
+    loadw(wb, cc + 1);
+    consume(wa, cc);
+    loadw(wa, cc + 2);
+    consume(wb, cc + 1);
+  }
+  const double sres = reduce8(acc, lane);
+  const int i = (lane >> 2) & 7;
+  if ((lane & 3) == 0 && i < pn.cnt) zpart[i * kZStride + warp] = sres;
+}
+
 // Row tasks over the own panel.
 //   UPD 0: z_i = S[r,:].x + sum_{j<mcorr} us[i][j] coef[j]   (read-only; us == nullptr: plain)
 //   UPD 1: w += lr*dsl[i] * x ; z_i = w.x                     (immediate update; kept for layers
@@ -393,10 +454,12 @@ template <int UPD>
 __device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
                                            int act_kind, const Dst &dst, int segs, double *zpart, const double *us,
                                            const double *coef, int mcorr, int m, const DotOut &dots, double *red,
-                                           double *ykeep = nullptr) {
+                                           double *ykeep = nullptr, bool z_ready = false) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int nz;  // partials per row
-  if (ld >= 4 * kPanelCols) {
+  if (z_ready) {  // panel_z_chunks has filled zpart[i][0..kWarps)
+    nz = kWarps;
+  } else if (ld >= 4 * kPanelCols) {
     panel_z_stream<UPD>(W, ld, pn, xs, dsl, lr, zpart);
     nz = kWarps;
   } else {
@@ -631,13 +694,26 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
         for (int q = 0; q < n.world; ++q) stg_cg(n.arena[q] + off, zs[threadIdx.x]);
     }
   };
+  // layer l >= 1 consumes its input slice by slice (panel_z_chunks) instead of behind a full cross-rank barrier
+  auto slice_ok = [&](int l) -> bool {
+    return !TG && p.slicewise && multi && l >= 1 && l < NLw &&
+           panel_max((n.dims[l + 1] + n.world - 1) / n.world, grid) <= 8;
+  };
   auto forward = [&](int l, int src_buf, int dst_buf, int m, unsigned long long tag) {
-    stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
-    __syncthreads();
-    trace(600 + l);  // input vector staged (tagged mode: every producer's value has arrived)
-    if (l >= 1 && m > 0) {  // coef[j] = v_j . x
-      if (tg) gather_dots_tagged(n, l, m, tag, coef, red, grid);
-      else gather_dots(n, l, m, coef, red, grid);
+    const bool sw = slice_ok(l);
+    if (sw) {
+      trace(600 + l);
+      panel_z_chunks(n.W[l], n.ld[l], panel(l), act_of(l, src_buf), n, l, bar, rowpart);
+      __syncthreads();  // every warp has seen every rank's flag: the whole input (and the dot-product chunks) is there
+      if (m > 0) gather_dots(n, l, m, coef, red, grid);
+    } else {
+      stage_act(xs, l, src_buf, tag);  // produced earlier in the same sweep
+      __syncthreads();
+      trace(600 + l);  // input vector staged (tagged mode: every producer's value has arrived)
+      if (l >= 1 && m > 0) {  // coef[j] = v_j . x
+        if (tg) gather_dots_tagged(n, l, m, tag, coef, red, grid);
+        else gather_dots(n, l, m, coef, red, grid);
+      }
     }
     trace(700 + l);  // partial dot products gathered
     Dst dst;  // all-gather by peer stores
@@ -662,13 +738,18 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     const int segs = pick_row_segments(n.rows[l], n.ld[l], grid);
     const bool feeds_out = fold && l == NL - 2;
     panel_rows<0>(n.W[l], n.ld[l], panel(l), xs, dsl, p.lr, kind, dst, segs, rowpart, us_of(l),
-                  l == 0 ? coef0 : coef, l == 0 ? 1 : m, m, dots, red, feeds_out ? ylast : nullptr);
+                  l == 0 ? coef0 : coef, l == 0 ? 1 : m, m, dots, red, feeds_out ? ylast : nullptr, sw);
     if (feeds_out) fold_publish();
+  };
+  // barrier after the forward pass of layer l: only the arrive half when the next layer waits per producer rank
+  auto forward_sync = [&](int l) {
+    if (slice_ok(l + 1)) bar.arrive_all(n);
+    else phase_sync(panel(l).cnt > 0);
   };
 
   for (int l = 0; l < NLw; ++l) {
     forward(l, cur, cur, 0, tag_of(0));
-    phase_sync(panel(l).cnt > 0);
+    forward_sync(l);
   }
   const double *target = A + n.off_target;
   const int last = NLw - 1;  // top-most layer with phases of its own
@@ -906,13 +987,13 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
     forward(0, 0, cur ^ 1, m, tag);  // (stages x and synchronises before ubar is read)
     trace(300);
     prefetch_panel(1);
-    phase_sync(panel(0).cnt > 0);
+    forward_sync(0);
     trace(400);
     for (int l = 1; l < NLw; ++l) {
       forward(l, cur ^ 1, cur ^ 1, m, tag);
       trace(300 + l);
       prefetch_panel(l + 1 < NLw ? l + 1 : last - 1);  // after the last layer: the first wide top-down pass
-      phase_sync(panel(l).cnt > 0);
+      forward_sync(l);
       trace(400 + l);
     }
     cur ^= 1;
@@ -1073,6 +1154,11 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
       widest = bytes > widest ? bytes : widest;
     }
     p.keep_l2 = keep_env >= 0 ? (keep_env ? 1 : 0) : (widest <= (80LL << 20) ? 1 : 0);
+    static const int slice_env = [] {
+      const char *e = getenv("HPNN_SLICEWISE");
+      return (e && !strcmp(e, "0")) ? 0 : 1;
+    }();
+    p.slicewise = (slice_env && !p.tagged && n.world > 1) ? 1 : 0;
     p.fold_out = (fold_env && !p.tagged && n.off_zpart > 0 && n.dims[n.n_layers] <= kFoldMaxOut && n.n_layers >= 3) ? 1 : 0;
   }
   p_out = p;

@@ -421,6 +421,7 @@ static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
   p.lazy_depth = 0;
   p.prefetch_bytes = 0;
   p.fold_out = 0;
+  p.slicewise = 0;
   p.keep_l2 = 0;
   {
     static const long long env_ms = [] {

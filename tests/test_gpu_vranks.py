@@ -50,8 +50,10 @@ def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto, train):
     lib.hpnn_dev_set_lazy(8, 0)
     lib.hpnn_dev_set_lazy_panel(1)
     try:
-        for nn_type in (N.TYPE_ANN, N.TYPE_SNN):
-            n_in, hid, n_out = 40, (600, 300, 150), 12
+        # the second shape has a 2600-wide input to its second layer: three 1024-column chunks in the
+        # slice-by-slice forward pass, whose columns come from several producer ranks each
+        for nn_type, (n_in, hid, n_out) in ((N.TYPE_ANN, (40, (600, 300, 150), 12)), (N.TYPE_SNN, (40, (600, 300, 150), 12)),
+                                            (N.TYPE_ANN, (24, (2600, 40), 10))):
             k, _ = hp.generate_kernel(77, n_in, list(hid), n_out)
             X, T = make_problem(nn_type, n_in, hid, n_out, n_samples=2, seed=3)
             n_it = 19
