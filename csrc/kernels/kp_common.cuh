@@ -161,15 +161,16 @@ struct Barrier {
     __syncthreads();
   }
   // CTA 0, after its fence.sys: this rank's flag word (= kx) and +1 on the barrier counter, on every rank
-  __device__ __forceinline__ void signal(const hpnn_dev_net &n) {
+  // (with_flag: the per-rank flag is only read by wait_rank, i.e. after an arrive_all)
+  __device__ __forceinline__ void signal(const hpnn_dev_net &n, bool with_flag = false) {
     if (n.arena_mc) {
       unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena_mc + n.off_flags);
-      multimem_st_u64(f + n.rank, (unsigned long long)kx);
+      if (with_flag) multimem_st_u64(f + n.rank, (unsigned long long)kx);
       multimem_red_add_u64(f + kCounterSlot, 1ull);
     } else {
       for (int q = 0; q < n.world; ++q) {
         unsigned long long *f = reinterpret_cast<unsigned long long *>(n.arena[q] + n.off_flags);
-        st_relaxed_sys(f + n.rank, (unsigned long long)kx);
+        if (with_flag) st_relaxed_sys(f + n.rank, (unsigned long long)kx);
         red_add_relaxed_sys_u64(f + kCounterSlot, 1ull);
       }
     }
@@ -195,7 +196,7 @@ struct Barrier {
         }
         *prev = 0;
         fence_sys();
-        signal(n);
+        signal(n, true);
       }
     }
     __syncthreads();

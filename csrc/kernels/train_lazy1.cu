@@ -1103,6 +1103,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_train_sample_lazy1_vranks(const
 }
 
 int g_lazy_panel = -1;  // -1 = HPNN_LAZY_PANEL (default on), 0 = off, 1 = on
+int g_slicewise = -1;   // -1 = HPNN_SLICEWISE (default off), 0 = off, 1 = on
 // Eligibility + launch parameters of K-PL1 for one rank: 0 = p_out / smem_out filled, 1 = not eligible.
 int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
   static const int disabled_env = [] {
@@ -1154,11 +1155,16 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
       widest = bytes > widest ? bytes : widest;
     }
     p.keep_l2 = keep_env >= 0 ? (keep_env ? 1 : 0) : (widest <= (80LL << 20) ? 1 : 0);
+    // Measured at 8 GPUs on the wide shape (profiles/r2_probe8e_*.jsonl): 234 us/iteration against 190 with the
+    // full barrier.  Every rank's flag arrives at about the same time, so only the two chunks of weights
+    // that are in flight during the wait overlap it, and the chunked pass itself streams at 2.1 TB/s
+    // (eight rows x 16 bytes per thread and chunk) against 4.9 TB/s.  Off unless HPNN_SLICEWISE=1.
     static const int slice_env = [] {
       const char *e = getenv("HPNN_SLICEWISE");
-      return (e && !strcmp(e, "0")) ? 0 : 1;
+      return (e && !strcmp(e, "1")) ? 1 : 0;
     }();
-    p.slicewise = (slice_env && !p.tagged && n.world > 1) ? 1 : 0;
+    const int slice_on = g_slicewise >= 0 ? g_slicewise : slice_env;
+    p.slicewise = (slice_on && !p.tagged && n.world > 1) ? 1 : 0;
     p.fold_out = (fold_env && !p.tagged && n.off_zpart > 0 && n.dims[n.n_layers] <= kFoldMaxOut && n.n_layers >= 3) ? 1 : 0;
   }
   p_out = p;
@@ -1208,3 +1214,4 @@ int launch_lazy1_vranks(const KP *pv_dev, int world, int ctas_per_rank, bool tag
 }  // namespace hpnn
 
 extern "C" void hpnn_dev_set_lazy_panel(int on) { hpnn::g_lazy_panel = on < 0 ? -1 : (on ? 1 : 0); }
+extern "C" void hpnn_dev_set_slicewise(int on) { hpnn::g_slicewise = on < 0 ? -1 : (on ? 1 : 0); }

@@ -116,6 +116,7 @@ def _declare(lib):
         "hpnn_dev_set_persistent_grid": (None, [i]),
         "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),
         "hpnn_dev_set_lazy_panel": (None, [i]),
+        "hpnn_dev_set_slicewise": (None, [i]),
         "hpnn_abi_sizeof": (C.c_longlong, [i]),
         "hpnn_dev_set_phase_trace": (None, [vp, i]),
         "hpnn_dev_forward_layer": (i, [vp, i, i, i, vp, vp, i, vp]),

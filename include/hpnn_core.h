@@ -197,6 +197,9 @@ void hpnn_dev_set_lazy(int depth, long long min_bytes);
 /* one rank only: row-panel organisation of the same trainer (train_lazy1.cu); 1 = on, 0 = off
  * (column tasks, train_lazy.cu), -1 = default (on unless HPNN_LAZY_PANEL=0) */
 void hpnn_dev_set_lazy_panel(int on);
+/* several ranks, panels of at most 8 rows: forward passes wait per producer rank inside the pass instead of behind
+ * a full cross-rank barrier; 1 = on, 0 = off, -1 = default (off unless HPNN_SLICEWISE=1: measured slower) */
+void hpnn_dev_set_slicewise(int on);
 
 /* fills ld/row0/rows/offsets from dims/rank/world; returns arena size in doubles */
 long long hpnn_dev_arena_layout(hpnn_dev_net *net);

@@ -39,14 +39,17 @@ def test_streaming_trainer_on_virtual_ranks(monkeypatch, world, proto, nn_type, 
 
 
 @pytest.mark.parametrize("train", [N.TRAIN_BP, N.TRAIN_BPM])
-@pytest.mark.parametrize("proto", ["barrier", "tagged"])
+@pytest.mark.parametrize("proto", ["barrier", "tagged", "barrier-slicewise"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto, train):
     """K-PL1 with several ranks: per-rank column-slice sums scattered to the owning rank, forward
     results and partial dot products stored into every rank's arena; 19 iterations = two
     write-back periods of 8 plus a partial one."""
-    monkeypatch.setenv("HPNN_TP_PROTOCOL", proto)
+    # "barrier-slicewise": the opt-in forward pass that waits per producer rank (HPNN_SLICEWISE is read once
+    # per process, so the variant is selected through the setter)
+    monkeypatch.setenv("HPNN_TP_PROTOCOL", proto.split("-")[0])
     lib = N.load()
+    lib.hpnn_dev_set_slicewise(1 if proto.endswith("slicewise") else 0)
     lib.hpnn_dev_set_lazy(8, 0)
     lib.hpnn_dev_set_lazy_panel(1)
     try:
@@ -70,6 +73,7 @@ def test_row_panel_trainer_on_virtual_ranks(monkeypatch, world, proto, train):
             eng.close()
             cpu.close()
     finally:
+        lib.hpnn_dev_set_slicewise(-1)
         lib.hpnn_dev_set_lazy(-1, -1)
         lib.hpnn_dev_set_lazy_panel(-1)
 
