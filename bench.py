@@ -229,6 +229,7 @@ def run_ours(args, cfg):
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     res_dev = eng.net.fetch_results(len(timed))
     iters_dev = sum(r.n_iter for r in res_dev)
+    split_world = eng.net.world  # 1 when the net is too small to be worth splitting (every rank holds all of it)
     clk = clocks.stop() if rank == 0 else None
     eng.close()
 
@@ -268,8 +269,12 @@ def run_ours(args, cfg):
             "config": config_block(args, cfg, world),
             "detail": {"iterations_timed": iters_dev, "iterations_per_s": iters_dev / (dev_ms * 1e-3),
                        "samples_converged": n_ok, "us_per_iteration": dev_ms * 1e3 / max(1, iters_dev),
-                       "engine": "one process per GPU, one cooperative kernel launch per sample; all-gather / "
-                                 "reduce-scatter by peer stores from inside the kernel"},
+                       "engine": ("one process per GPU, one cooperative kernel launch per sample; rows split over %d ranks, "
+                                  "all-gather / reduce-scatter by peer or NVLS multicast stores from inside the kernel" % split_world)
+                       if split_world > 1 else
+                       ("one cooperative kernel launch per sample on one GPU" + ("" if world == 1 else
+                        "; the net is below HPNN_TP_MIN_MB, so each of the %d ranks holds all of it and trains the same "
+                        "samples (row-splitting it over NVLink is slower)" % world))},
             "clocks": clk,
             "e2e": {"value": K / (e2e_ms * 1e-3), "unit": "samples/s",
                     "h2d_bytes_per_step": 8 * (n_in + n_out), "d2h_bytes_per_step": C.sizeof(N.TrainResult),

@@ -181,6 +181,9 @@ def test_arena_layout_regions_are_disjoint_and_cover_the_variants():
                          ("hd%d" % l, net.off_hist_dot[l], 2 * 8 * W * 160)]
             if net.panel_stride:
                 regs.append(("panel", net.off_panel, 2 * 160 * net.panel_stride))
+        if net.off_zpart:  # folded output layer: working copies of the layer and its momentum, partial output sums
+            wl = pad(net.dims[NL] * net.ld[NL - 1])
+            regs += [("wlast", net.off_wlast, wl), ("mlast", net.off_mlast, wl), ("zpart", net.off_zpart, W * 160 * 32)]
         return regs
 
     def check(net, total):
@@ -197,7 +200,11 @@ def test_arena_layout_regions_are_disjoint_and_cover_the_variants():
             wide, total = layout([784, 8192, 8192, 8192, 8192, 10], rank, world)
             assert wide.hist_depth == 8 and wide.panel_stride == 8192 + 8 and wide.cta_slots == 0
             assert wide.rows[1] == 8192 // world and wide.row0[1] == rank * (8192 // world)
+            assert wide.off_wlast > 0 and wide.off_mlast > wide.off_wlast and wide.off_zpart > wide.off_mlast
             check(wide, total)
+    many_out, total = layout([784, 8192, 8192, 64], 0, 2)  # more than 32 outputs: the output layer is not folded
+    assert many_out.hist_depth == 8 and many_out.off_zpart == 0
+    check(many_out, total)
     # the history threshold is a setting (tests use it to exercise the deferred-update trainers on small nets)
     lib.hpnn_dev_set_lazy(-1, 0)
     try:
