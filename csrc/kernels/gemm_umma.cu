@@ -13,11 +13,21 @@
 //   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 columns per instruction), activation in
 //               fp32 (the operands were bf16 anyway), direct stores widened to FP64.
 // Out-of-range rows/columns of partial tiles are zero-filled by TMA and masked at the store.
+//
+// CL = 2: two CTAs of a thread-block cluster work on the two 128-row batch tiles that share one 256-row
+// block of W.  Each CTA fetches HALF of that W block per k-step and the TMA multicasts it into both
+// CTAs' rings (cp.async.bulk.tensor ... .multicast::cluster), so a k-step costs 32 KB of L2 reads per SM
+// instead of 48 KB -- the ring was waiting on L2, not on the tensor pipe.  A ring slot is released by
+// BOTH CTAs' MMA warps (tcgen05.commit ... .multicast::cluster on a 2-count mbarrier), because a slot
+// now also receives the peer's half.  The tensor maps of this kernel cover operands in this GPU's own
+// memory only (launch_umma checks the pointers and otherwise takes the CL = 1 kernel): TMA multicast loads
+// here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "dev_common.cuh"
 
@@ -67,6 +77,31 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
       "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// the same load, delivered to the same shared-memory offset (and mbarrier) of every CTA in `mask`
+__device__ __forceinline__ void tma_load_2d_mc(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1,
+                                               uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, "
+      "%4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// 2/(1+e^-z) - 1 == tanh(z/2): one MUFU operation instead of two (the bf16-output epilogue is MUFU-bound;
+// tanh.approx is good to about 2^-11, the bf16 result keeps 2^-8)
+__device__ __forceinline__ float ann_act_f32(float z) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(0.5f * z));
+  return y;
+}
 // K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   uint64_t d = 0;
@@ -89,6 +124,13 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// arrives on the mbarrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void umma_commit_mc(uint64_t *bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
                : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
@@ -125,7 +167,7 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: 
 // boundaries.  OUT_BF16: hidden layers hand bf16 activations straight to the next layer's GEMM -- the tile is
 // staged in shared memory in the 128-byte-swizzle layout (conflict-free 16-byte stores) and leaves
 // through two TMA stores; otherwise FP64 results are stored directly (the last layer, 10..230 wide).
-template <bool OUT_BF16>
+template <bool OUT_BF16, int CL>
 __global__ void __launch_bounds__(THREADS, 1)
     k_gemm_bf16_umma(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                      const __grid_constant__ CUtensorMap map_y, int batch, int rows, int k_total, double *__restrict__ Y,
@@ -140,7 +182,11 @@ __global__ void __launch_bounds__(THREADS, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = (k_total + BK - 1) / BK;
   const int ntn = (rows + BN - 1) / BN, ntm = (batch + BM - 1) / BM;
-  const int ntiles = ntn * ntm;
+  // CL == 2: the cluster walks over pairs of batch tiles; CTA `crank` takes tile 2 * pair + crank
+  const int crank = CL == 2 ? (int)cluster_ctarank() : 0;
+  const int ntiles = CL == 2 ? ntn * ((ntm + 1) / 2) : ntn * ntm;
+  const int first = CL == 2 ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int step = CL == 2 ? (int)gridDim.x / 2 : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
@@ -148,7 +194,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     if (OUT_BF16) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_y)) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], 1);
+      mbar_init(&empty[s], CL);  // released by the MMA warp of every CTA that reads (part of) this slot
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
@@ -164,14 +210,15 @@ __global__ void __launch_bounds__(THREADS, 1)
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // the peer's barriers exist before anything is multicast to them
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     if (lane == 0) {  // TMA producer: one ring for all tiles of this CTA
       int it = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const int m0 = (t / ntn) * BM, n0 = (t % ntn) * BN;
+      for (int t = first; t < ntiles; t += step) {
+        const int m0 = ((t / ntn) * CL + crank) * BM, n0 = (t % ntn) * BN;
         for (int kb = 0; kb < nk; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
@@ -179,14 +226,17 @@ __global__ void __launch_bounds__(THREADS, 1)
           mbar_expect_tx(&full[s], STAGE_BYTES);
           uint8_t *a = smem + s * STAGE_BYTES;
           tma_load_2d(a, &map_x, &full[s], kb * BK, m0);
-          tma_load_2d(a + A_BYTES, &map_w, &full[s], kb * BK, n0);
+          if (CL == 2)  // my half of the W block, into both CTAs
+            tma_load_2d_mc(a + A_BYTES + crank * (B_BYTES / 2), &map_w, &full[s], kb * BK, n0 + crank * (BN / 2), 0x3);
+          else
+            tma_load_2d(a + A_BYTES, &map_w, &full[s], kb * BK, n0);
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {  // MMA issuer
       int it = 0, i = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
+      for (int t = first; t < ntiles; t += step, ++i) {
         const int acc = i & 1;
         mbar_wait(&tmem_empty[acc], ((i >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -203,7 +253,8 @@ __global__ void __launch_bounds__(THREADS, 1)
             // advancing K inside the swizzle atom = +32 bytes on the start address field
             umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), kIdesc, (kb | k) ? 1u : 0u);
           }
-          umma_commit(&empty[s]);                          // slot reusable once these MMAs have read it
+          if (CL == 2) umma_commit_mc(&empty[s], 0x3);     // slot reusable once BOTH CTAs' MMAs have read it
+          else umma_commit(&empty[s]);                     // slot reusable once these MMAs have read it
           if (kb == nk - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
         }
       }
@@ -213,8 +264,8 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int q = warp & 3;
     const int et = threadIdx.x - 64;  // 0..127
     int i = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++i) {
-      const int m0 = (t / ntn) * BM, n0 = (t % ntn) * BN;
+    for (int t = first; t < ntiles; t += step, ++i) {
+      const int m0 = ((t / ntn) * CL + crank) * BM, n0 = (t % ntn) * BN;
       const int acc = i & 1;
       mbar_wait(&tmem_full[acc], (i >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -242,8 +293,8 @@ __global__ void __launch_bounds__(THREADS, 1)
             for (int e = 0; e < 4; ++e) {
               float z0 = __uint_as_float(v[j * 8 + 2 * e]), z1 = __uint_as_float(v[j * 8 + 2 * e + 1]);
               if (act_kind == 0) {
-                z0 = __fdividef(2.0f, 1.0f + __expf(-z0)) - 1.0f;
-                z1 = __fdividef(2.0f, 1.0f + __expf(-z1)) - 1.0f;
+                z0 = ann_act_f32(z0);
+                z1 = ann_act_f32(z1);
               }
               __nv_bfloat162 h = __floats2bfloat162_rn(z0, z1);
               pk[e] = *reinterpret_cast<uint32_t *>(&h);
@@ -281,6 +332,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // nobody leaves while the peer may still signal its barriers
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS)
                  : "memory");
@@ -360,18 +412,58 @@ struct MapKey {
     return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box == o.box;
   }
 };
-static const CUtensorMap *cached_map(const void *base, int rows, int cols, int ld, int box_rows) {
+struct MapEntry {
+  CUtensorMap map;
+  bool local;  // the operand is an allocation of the current device (not a peer mapping, not host memory)
+};
+// cudaMalloc / torch allocations of the current device only; anything else (peer mappings through IPC or
+// the VMM API, managed or host memory) answers false and keeps the multicast kernel away from it.
+static bool memory_of_this_device(const void *p) {
+  cudaPointerAttributes a;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice && a.device == dev;
+}
+static const MapEntry *cached_map(const void *base, int rows, int cols, int ld, int box_rows) {
   constexpr int kSlots = 64;
   static MapKey keys[kSlots];
-  static CUtensorMap maps[kSlots];
+  static MapEntry maps[kSlots];
   static int used = 0, next = 0;
   const MapKey k{base, rows, cols, ld, box_rows};
   for (int i = 0; i < used; ++i)
     if (keys[i] == k) return &maps[i];
   const int slot = used < kSlots ? used++ : (next++ % kSlots);
-  if (!umma::make_map(&maps[slot], base, rows, cols, ld, box_rows)) return nullptr;
+  keys[slot] = MapKey{nullptr, 0, 0, 0, 0};
+  if (!umma::make_map(&maps[slot].map, base, rows, cols, ld, box_rows)) return nullptr;
+  maps[slot].local = memory_of_this_device(base);
   keys[slot] = k;
   return &maps[slot];
+}
+
+static int g_kt_cluster = -1;  // -1: environment HPNN_KT_CLUSTER (default on), 0 / 1: set by hpnn_dev_set_kt_cluster
+
+// largest number of co-resident 2-CTA clusters of kernel `kfn` (0: cluster launch unavailable)
+static int max_clusters(const void *kfn) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2, 1, 1);
+  cfg.blockDim = dim3(umma::THREADS, 1, 1);
+  cfg.dynamicSmemBytes = umma::SMEM_BYTES;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kfn, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
 }
 
 static int launch_umma(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y, int ldy,
@@ -380,40 +472,110 @@ static int launch_umma(const void *Wb, int ldw, int rows, int cols, const void *
     set_error_msg("hpnn_dev_gemm_bf16: operands must be 16-byte aligned with leading dimensions % 8 == 0");
     return -1;
   }
-  const CUtensorMap *mx = cached_map(Xb, batch, cols, ldx, umma::BM), *mw = cached_map(Wb, rows, cols, ldw, umma::BN);
-  const CUtensorMap *my = Yb ? cached_map(Yb, batch, rows, ldyb, umma::BM) : mx;
-  if (!mx || !mw || !my) {
-    set_error_msg("hpnn_dev_gemm_bf16: cuTensorMapEncodeTiled failed");
-    return -1;
+  if (g_kt_cluster < 0) {
+    const char *e = getenv("HPNN_KT_CLUSTER");
+    g_kt_cluster = (e && e[0] == '0') ? 0 : 1;
   }
-  static int sms = 0;
+  static int sms = 0, pairs_bf16 = -1, pairs_f64 = -1;
   if (!sms) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   }
-  const int ntiles = ((rows + umma::BN - 1) / umma::BN) * ((batch + umma::BM - 1) / umma::BM);
-  const int grid = ntiles < sms ? ntiles : sms;
-  const void *kfn = Yb ? (const void *)umma::k_gemm_bf16_umma<true> : (const void *)umma::k_gemm_bf16_umma<false>;
-  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, umma::SMEM_BYTES);
-  if (e != cudaSuccess) {
-    set_error("cudaFuncSetAttribute(k_gemm_bf16_umma)", e);
+  const void *k1 = Yb ? (const void *)umma::k_gemm_bf16_umma<true, 1> : (const void *)umma::k_gemm_bf16_umma<false, 1>;
+  const void *k2 = Yb ? (const void *)umma::k_gemm_bf16_umma<true, 2> : (const void *)umma::k_gemm_bf16_umma<false, 2>;
+  static bool attr_set[4] = {false, false, false, false};
+  const int vi = Yb ? 0 : 1;
+  if (!attr_set[vi]) {
+    cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, umma::SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, umma::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(k_gemm_bf16_umma)", e);
+      return -1;
+    }
+    attr_set[vi] = true;
+  }
+  int &pairs = Yb ? pairs_bf16 : pairs_f64;
+  if (pairs < 0) pairs = max_clusters(k2);
+  const int ntn = (rows + umma::BN - 1) / umma::BN, ntm = (batch + umma::BM - 1) / umma::BM;
+  // the pair kernel pays when there are at least two batch tiles to pair and all operands live on this GPU
+  bool pair = g_kt_cluster == 1 && pairs > 0 && ntm >= 2;
+  // entries are copied out at once: a later miss may recycle the slot an earlier hit pointed to
+  MapEntry ex, ey, ew;
+  const MapEntry *q = cached_map(Xb, batch, cols, ldx, umma::BM);
+  bool ok = q != nullptr;
+  if (ok) ex = *q;
+  ey = ex;
+  if (ok && Yb) {
+    q = cached_map(Yb, batch, rows, ldyb, umma::BM);
+    ok = q != nullptr;
+    if (ok) ey = *q;
+  }
+  if (ok && pair) {
+    q = cached_map(Wb, rows, cols, ldw, umma::BN / 2);
+    ok = q != nullptr;
+    if (ok) ew = *q;
+    pair = ok && ex.local && ey.local && ew.local;
+  }
+  if (ok && !pair) {
+    q = cached_map(Wb, rows, cols, ldw, umma::BN);
+    ok = q != nullptr;
+    if (ok) ew = *q;
+  }
+  if (!ok) {
+    set_error_msg("hpnn_dev_gemm_bf16: cuTensorMapEncodeTiled failed");
     return -1;
   }
-  if (Yb)
-    umma::k_gemm_bf16_umma<true><<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(*mx, *mw, *my, batch, rows,
-                                                                                               cols, nullptr, 0, act_kind);
-  else
-    umma::k_gemm_bf16_umma<false><<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(*mx, *mw, *my, batch, rows,
-                                                                                                cols, Y, ldy, act_kind);
-  e = cudaGetLastError();
-  if (e != cudaSuccess) {
-    set_error("k_gemm_bf16_umma", e);
-    return -1;
+  const MapEntry *mx = &ex, *my = &ey, *mw = &ew;
+  cudaError_t e;
+  if (pair) {
+    const int npairs = ntn * ((ntm + 1) / 2);
+    const int ncl = npairs < pairs ? npairs : pairs;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * ncl, 1, 1);
+    cfg.blockDim = dim3(umma::THREADS, 1, 1);
+    cfg.dynamicSmemBytes = umma::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    double *y = Yb ? nullptr : Y;
+    int ldy_ = Yb ? 0 : ldy;
+    if (Yb)
+      e = cudaLaunchKernelEx(&cfg, umma::k_gemm_bf16_umma<true, 2>, mx->map, mw->map, my->map, batch, rows, cols, y, ldy_,
+                             act_kind);
+    else
+      e = cudaLaunchKernelEx(&cfg, umma::k_gemm_bf16_umma<false, 2>, mx->map, mw->map, my->map, batch, rows, cols, y, ldy_,
+                             act_kind);
+    if (e != cudaSuccess) {
+      set_error("k_gemm_bf16_umma (cluster launch)", e);
+      return -1;
+    }
+  } else {
+    const int ntiles = ntn * ntm;
+    const int grid = ntiles < sms ? ntiles : sms;
+    if (Yb)
+      umma::k_gemm_bf16_umma<true, 1><<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(
+          mx->map, mw->map, my->map, batch, rows, cols, nullptr, 0, act_kind);
+    else
+      umma::k_gemm_bf16_umma<false, 1><<<grid, umma::THREADS, umma::SMEM_BYTES, (cudaStream_t)stream>>>(
+          mx->map, mw->map, my->map, batch, rows, cols, Y, ldy, act_kind);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) {
+      set_error("k_gemm_bf16_umma", e);
+      return -1;
+    }
   }
   ++g_launches;
   return 0;
 }
+
+// 1: pairs of CTAs share each W block through TMA multicast (default), 0: one CTA per tile, -1: environment
+void hpnn_dev_set_kt_cluster(int on) { g_kt_cluster = on < 0 ? -1 : (on ? 1 : 0); }
 
 // Wb: [rows x ldw] bf16, Xb: [batch x ldx] bf16 (ldw, ldx multiples of 8, base 16-byte aligned); FP64 result
 int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, double *Y,

@@ -328,6 +328,9 @@ int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *
 /* same GEMM with a bf16 result [batch x ldyb] that feeds the next layer's GEMM directly (hidden layers) */
 int hpnn_dev_gemm_bf16_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, void *Yb,
                             int ldyb, int act_kind, void *stream);
+/* K-T on pairs of CTAs that share each block of W through TMA multicast within a thread-block cluster
+ * (operands in this GPU's memory only): 1 on (default), 0 off, -1 environment HPNN_KT_CLUSTER */
+void hpnn_dev_set_kt_cluster(int on);
 /* row-wise softmax exp(z-1)/(TINY+sum) on a [batch x n] matrix (in place) */
 int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void *stream);
 

@@ -14,10 +14,22 @@ def _rand(*shape, seed=0):
     return (torch.rand(*shape, generator=g, dtype=torch.float64) * 2 - 1).cuda()
 
 
+@pytest.fixture(params=[1, 0], ids=["pairs", "single"])
+def kt_cluster(request):
+    """Both tile mappings of K-T: pairs of CTAs sharing each block of W through TMA multicast (default
+    for two or more batch tiles), and one CTA per tile."""
+    from hpnn_b200 import _native as N
+
+    lib = N.load()
+    lib.hpnn_dev_set_kt_cluster(request.param)
+    yield request.param
+    lib.hpnn_dev_set_kt_cluster(-1)
+
+
 @pytest.mark.parametrize("batch,rows,cols", [(128, 128, 64), (128, 128, 256), (1, 10, 1000), (333, 230, 851),
                                              (4096, 1000, 784), (257, 1000, 1000)])
 @pytest.mark.parametrize("act_kind", [0, 1])
-def test_gemm_bf16_umma(batch, rows, cols, act_kind):
+def test_gemm_bf16_umma(batch, rows, cols, act_kind, kt_cluster):
     from hpnn_b200.ops import cuda as ops
 
     W = _rand(rows, cols, seed=1) / np.sqrt(cols)
@@ -48,9 +60,9 @@ def test_forward_batch_bf16_close_to_fp64():
 
 
 @pytest.mark.parametrize("batch,rows,cols", [(128, 128, 64), (100, 70, 40), (333, 230, 851), (4096, 1000, 784),
-                                             (8192, 2048, 512)])
+                                             (8192, 2048, 512), (8192 + 128, 520, 192)])
 @pytest.mark.parametrize("act_kind", [0, 1])
-def test_gemm_bf16_chain_output(batch, rows, cols, act_kind):
+def test_gemm_bf16_chain_output(batch, rows, cols, act_kind, kt_cluster):
     """bf16-in / bf16-out variant (hidden layers of the tensor-core chain): persistent tile loop, two TMEM
     accumulators, swizzled staging + TMA store.  The largest shape gives every CTA about seven tiles."""
     from hpnn_b200.ops import cuda as ops
