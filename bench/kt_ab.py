@@ -38,7 +38,7 @@ def main():
         H1 = ops.gemm_bf16_chain(Wb[0], Xs[0], 784, 0)
         out = {"batch": B, "input_buffers": nbuf}
         ref = None
-        for mode, name in ((0, "single"), (1, "pairs")):
+        for mode, name in ((0, "single"), (1, "pair_multicast"), (2, "pair_mma")):
             lib.hpnn_dev_set_kt_cluster(mode)
             t_hidden = timed(lambda: ops.gemm_bf16_chain(Wb[1], H1, 1000, 0))
             k = [0]
@@ -59,6 +59,11 @@ def main():
             out[name] = {"hidden_gemm_us": round(t_hidden, 2), "hidden_gemm_tflops": round(flop / t_hidden / 1e6, 1),
                          "chain_us": round(t_chain, 2), "chain_samples_per_s": round(B / t_chain * 1e6)}
         lib.hpnn_dev_set_kt_cluster(-1)
+        # library GEMM on the same operands for scale (no activation, so less work): torch.matmul -> cuBLAS
+        Wt = Wb[1][:, :1000].t()
+        t_lib = timed(lambda: torch.matmul(H1[:, :1000], Wt))
+        out["torch_matmul_bf16_no_activation"] = {"hidden_gemm_us": round(t_lib, 2),
+                                                  "hidden_gemm_tflops": round(2.0 * B * 1e6 / t_lib / 1e6, 1)}
         print(json.dumps(out), flush=True)
 
 

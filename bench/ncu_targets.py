@@ -1,6 +1,6 @@
 """Short, single-purpose scenarios for `ncu --set full` (one GPU, few launches).
 
-    python bench/ncu_targets.py kt | kt_chain [batch] | kg | kp_wide | kpl1_wide | kp_snn_stream | kpr_snn | ops_wide"""
+    python bench/ncu_targets.py kt | kt_chain [batch ...] | kg | kp_wide | kpl1_wide | kp_snn_stream | kpr_snn | ops_wide"""
 import os
 import sys
 
@@ -29,12 +29,14 @@ def train_case(nn_type, train, n_in, hid, n_out, iters):
 def main():
     which = sys.argv[1]
     if which == "kt_chain":  # bf16-in / bf16-out hidden-layer GEMM (persistent, two TMEM accumulators, TMA store)
-        rows, cols, B = 1000, 1000, int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+        rows, cols = 1000, 1000
         W = torch.rand(rows, cols, dtype=torch.float64, device="cuda") - 0.5
-        X = torch.rand(B, cols, dtype=torch.float64, device="cuda")
-        Wb, Xb = ops.cast_bf16(ops.padded_weights(W), cols), ops.cast_bf16(X, cols)
-        for _ in range(4):
-            ops.gemm_bf16_chain(Wb, Xb, cols, 0)
+        Wb = ops.cast_bf16(ops.padded_weights(W), cols)
+        for B in ([int(a) for a in sys.argv[2:]] or [4096]):
+            X = torch.rand(B, cols, dtype=torch.float64, device="cuda")
+            Xb = ops.cast_bf16(X, cols)
+            for _ in range(3):
+                ops.gemm_bf16_chain(Wb, Xb, cols, 0)
         torch.cuda.synchronize()
     elif which in ("kt", "kg"):
         rows, cols, B = 1000, 1000, 4096

@@ -145,6 +145,7 @@ def _declare(lib):
         "hpnn_dev_gemm_bf16": (i, [vp, i, i, i, vp, i, i, vp, i, i, vp]),
         "hpnn_dev_gemm_bf16_bf16": (i, [vp, i, i, i, vp, i, i, vp, i, i, vp]),
         "hpnn_dev_set_kt_cluster": (None, [i]),
+        "hpnn_dev_set_kt_trace": (None, [vp]),
         "hpnn_net_forward_batch": (i, [vp, vp, i, vp, i]),
         "hpnn_dev_forward_noalloc": (i, [i, i, i, C.POINTER(i), C.POINTER(vp), vp, vp, vp]),
     }

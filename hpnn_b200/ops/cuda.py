@@ -126,11 +126,17 @@ def forward_batch(Wp: torch.Tensor, cols: int, X: torch.Tensor, act_kind: int = 
     return Y
 
 
+def pad64(v: int) -> int:
+    """Leading dimension of the bf16 operands of K-T: rows of 128-byte multiples, so that every 128-byte box row
+    of a TMA load or store is one cache line (with pad8 rows a box row straddles two lines: +25 % L2 sectors)."""
+    return (v + 63) & ~63
+
+
 def cast_bf16(A: torch.Tensor, cols: int) -> torch.Tensor:
-    """fp64 ``[R, >=cols]`` -> bf16 ``[R, pad8(cols)]`` (zero padded) with the native cast kernel."""
+    """fp64 ``[R, >=cols]`` -> bf16 ``[R, pad64(cols)]`` (zero padded) with the native cast kernel."""
     lib = N.load()
     rows = A.shape[0]
-    ld = (cols + 7) & ~7
+    ld = pad64(cols)
     out = torch.empty((rows, ld), dtype=torch.bfloat16, device=A.device)
     N.check(lib.hpnn_dev_cast_bf16(A.data_ptr(), A.stride(0), rows, cols, out.data_ptr(), ld, _s()), "hpnn_dev_cast_bf16")
     return out
@@ -148,11 +154,12 @@ def gemm_bf16(Wb: torch.Tensor, Xb: torch.Tensor, cols: int, Y: Optional[torch.T
 
 
 def gemm_bf16_chain(Wb: torch.Tensor, Xb: torch.Tensor, cols: int, act_kind: int = 0) -> torch.Tensor:
-    """K-T for hidden layers: bf16 in, bf16 out ``[B, pad8(N)]`` (activation in fp32), written by TMA
-    stores -- the result is the next layer's GEMM operand, no FP64 round trip and no cast kernel."""
+    """K-T for hidden layers: bf16 in, bf16 out ``[B, pad64(N)]`` (activation in fp32), written by TMA
+    stores -- the result is the next layer's GEMM operand, no FP64 round trip and no cast kernel.  The pad
+    columns are written by the kernel (zeros): no memset."""
     lib = N.load()
     rows, B = Wb.shape[0], Xb.shape[0]
-    Yb = torch.zeros((B, (rows + 7) & ~7), dtype=torch.bfloat16, device=Wb.device)  # pad columns stay zero
+    Yb = torch.empty((B, pad64(rows)), dtype=torch.bfloat16, device=Wb.device)
     N.check(lib.hpnn_dev_gemm_bf16_bf16(Wb.data_ptr(), Wb.stride(0), rows, cols, Xb.data_ptr(), Xb.stride(0), B,
                                         Yb.data_ptr(), Yb.stride(0), act_kind, _s()), "hpnn_dev_gemm_bf16_bf16")
     return Yb

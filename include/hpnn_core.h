@@ -328,9 +328,12 @@ int hpnn_dev_gemm_bf16(const void *Wb, int ldw, int rows, int cols, const void *
 /* same GEMM with a bf16 result [batch x ldyb] that feeds the next layer's GEMM directly (hidden layers) */
 int hpnn_dev_gemm_bf16_bf16(const void *Wb, int ldw, int rows, int cols, const void *Xb, int ldx, int batch, void *Yb,
                             int ldyb, int act_kind, void *stream);
-/* K-T on pairs of CTAs that share each block of W through TMA multicast within a thread-block cluster
- * (operands in this GPU's memory only): 1 on (default), 0 off, -1 environment HPNN_KT_CLUSTER */
-void hpnn_dev_set_kt_cluster(int on);
+/* tile mapping of K-T: 2 pairs of CTAs on one 256 x 256 tile (tcgen05.mma.cta_group::2, default), 1 pairs of
+ * CTAs that share each block of W through TMA multicast within a cluster, 0 one CTA per tile, -1 environment
+ * HPNN_KT_CLUSTER.  The pair mappings are used for operands in this GPU's own memory and two or more batch tiles. */
+void hpnn_dev_set_kt_cluster(int mode);
+/* diagnostic: CTA 0 of every following K-T launch writes clock64 stamps into buf (>= 160 int64 on the device); NULL: off */
+void hpnn_dev_set_kt_trace(void *buf);
 /* row-wise softmax exp(z-1)/(TINY+sum) on a [batch x n] matrix (in place) */
 int hpnn_dev_softmax_rows(double *Z, int ldz, int batch, int n, int stable, void *stream);
 
