@@ -46,7 +46,7 @@ def main():
     ms1 = timed(lambda: net.run(x1), n=200)
     out.append({"path": "ours K-P run (batch 1, fp64, H2D per sample)", "batch": 1, "samples_per_s": 1e3 / ms1})
     print(out[-1], flush=True)
-    for B in (1, 8, 64, 256, 1024, 4096):
+    for B in (1, 8, 64, 256, 1024, 4096, 16384):
         X = torch.from_numpy(rng.random((B, 784))).cuda()
         row = {"batch": B}
         row["ours_fp64_KG"] = B * 1e3 / timed(lambda: net.forward_batch(X))
