@@ -4,6 +4,9 @@ cycle trace of rank 0's CTA 0.  Per-iteration device time, max over the ranks of
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
         --master-port 29711 bench/scale_probe.py [config] [iterations] [worlds e.g. 8,4,2] [protocols]
+
+HPNN_TRACE_NS=1: the phase stamps are nanoseconds (%globaltimer) instead of SM cycles (the SM clock follows the power
+draw, so cycle counts of phases with different load are not comparable as times).
 """
 import json
 import os
@@ -23,6 +26,10 @@ from hpnn_b200.trainer import CudaEngine  # noqa: E402
 CFG = {
     "wide_ann": (hp.TYPE_ANN, hp.TRAIN_BP, 784, [8192, 8192, 8192, 8192], 10),
     "wide_ann_bpm": (hp.TYPE_ANN, hp.TRAIN_BPM, 784, [8192, 8192, 8192, 8192], 10),
+    # one GPU's view of the 8-rank job: 1024-row layers of 8192 columns = 7-row panels per CTA, no communication
+    "short_panels": (hp.TYPE_ANN, hp.TRAIN_BP, 784, [8192, 1024, 8192, 1024], 10),
+    "short_panels6": (hp.TYPE_ANN, hp.TRAIN_BP, 784, [8192, 1024, 8192, 1024, 8192, 1024], 10),
+    "wide6": (hp.TYPE_ANN, hp.TRAIN_BP, 784, [4096] * 6, 10),
     "snn_mnist": (hp.TYPE_SNN, hp.TRAIN_BPM, 784, [1000, 1000], 10),
     "xrd_snn": (hp.TYPE_SNN, hp.TRAIN_BPM, 851, [230], 230),
 }

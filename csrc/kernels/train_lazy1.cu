@@ -595,7 +595,10 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
   auto trace = [&](int tag) {
     if (p.trace && b == 0 && threadIdx.x == 0 && trace_n < p.trace_cap) {
       p.trace[2 * trace_n] = tag;
-      p.trace[2 * trace_n + 1] = clock64();
+      long long now;
+      if (p.trace_ns) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      else now = clock64();
+      p.trace[2 * trace_n + 1] = now;
       ++trace_n;
     }
   };

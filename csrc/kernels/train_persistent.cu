@@ -434,6 +434,13 @@ static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
   }
   p.trace = g_trace;
   p.trace_cap = g_trace_cap;
+  {
+    static const int ns_env = [] {
+      const char *e = getenv("HPNN_TRACE_NS");
+      return (e && e[0] == '1') ? 1 : 0;
+    }();
+    p.trace_ns = ns_env;  // SM cycles follow the clock, which moves with the power draw of the phase before
+  }
   int max_ld = 8, max_rows = 8;
   for (int l = 0; l < net->n_layers; ++l) {
     max_ld = net->ld[l] > max_ld ? net->ld[l] : max_ld;
