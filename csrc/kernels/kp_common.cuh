@@ -25,6 +25,7 @@ struct KP {
   hpnn_train_result *result;
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
+  int items_in_flight;  // row items (4 x 16 bytes per thread) the read-only top-down pass keeps in flight: 2 or 3
   int trace_ns;  // phase stamps in nanoseconds (%globaltimer) instead of SM cycles: HPNN_TRACE_NS=1
   int keep_l2;   // K-PL1: a rank's share of a layer fits L2, so the passes use caching loads instead of evict-first ones
   int slicewise;  // K-PL1, several ranks, short panels: forward passes consume the peers' activations slice by slice

@@ -85,8 +85,11 @@ constexpr int kPanelCols = 2 * kThreads;  // columns covered by one pass of the 
 
 // Read-only top-down pass over the own panel: four column chunks per thread, rows outermost, two
 // rows in flight.  Pout[c] = sum_i W[r0+i, c] * dsl[i].
-template <bool STREAM>
-__device__ __forceinline__ void panel_cols_read(const double *W, int ld, Panel pn, const double *dsl, double *Pout) {
+// Not inlined on purpose: inside the kernel body these loops share the 128 registers of a 512-thread CTA with
+// everything that is live around them; on their own they keep DEPTH items of G double2 in flight without spilling
+// (measured, profiles/r2_noinline_*.jsonl: 7-row panels 173.6 -> 166.9 us per iteration, 162.7 with DEPTH = 3).
+template <bool STREAM, int DEPTH>
+__device__ __noinline__ void panel_cols_read(const double *W, int ld, Panel pn, const double *dsl, double *Pout) {
   // The (column group, row) pairs form ONE software-pipelined sequence, two items in flight: with a
   // 7-row panel (8 ranks) a pipeline that restarted for every column group spent more time filling
   // and draining than streaming.
@@ -132,14 +135,16 @@ __device__ __forceinline__ void panel_cols_read(const double *W, int ld, Panel p
       ++cg;
     }
   };
-  double2 wa[G], wb[G];
+  double2 w[DEPTH][G];
   const int total = ng * pn.cnt;
-  load_next(wa);
-  for (int t = 0; t < total; t += 2) {
-    load_next(wb);
-    consume(wa);
-    load_next(wa);
-    consume(wb);
+#pragma unroll
+  for (int d = 0; d + 1 < DEPTH; ++d) load_next(w[d]);
+  for (int t = 0; t < total; t += DEPTH) {
+#pragma unroll
+    for (int d = 0; d < DEPTH; ++d) {
+      load_next(w[(d + DEPTH - 1) % DEPTH]);
+      consume(w[d]);
+    }
   }
 }
 
@@ -148,7 +153,7 @@ __device__ __forceinline__ void panel_cols_read(const double *W, int ld, Panel p
 //   P[c] from the OLD stored weights, then w += sum_{j<m} us[i][j] v_j[c] + (lr*d_i) h[c].
 // Pout == nullptr: final write-back, no sums wanted.
 template <bool HS>  // HS: h lives in shared memory
-__device__ __forceinline__ void panel_cols_flush(double *W, int ld, Panel pn, const double *dsl, const double *us,
+__device__ __noinline__ void panel_cols_flush(double *W, int ld, Panel pn, const double *dsl, const double *us,
                                                  const double *HV, const double *h, double lr, int m, double *Pout) {
   const double2 zero2 = make_double2(0.0, 0.0);
   const int mc = (m + 1) >> 1;
@@ -303,7 +308,7 @@ constexpr int kZStride = kWarps;  // partial dot products per row kept in shared
 // group; the per-row sums are completed inside each warp (reduce8) and parked per warp in
 // zpart[i*kZStride + warp] -- no CTA-wide barrier until the whole panel is done.
 template <int UPD>
-__device__ __forceinline__ void panel_z_stream(double *W, int ld, Panel pn, const double *xs, const double *dsl,
+__device__ __noinline__ void panel_z_stream(double *W, int ld, Panel pn, const double *xs, const double *dsl,
                                                double lr, double *zpart) {
   constexpr int G = 4;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -451,7 +456,7 @@ __device__ __forceinline__ void panel_z_chunks(const double *W, int ld, Panel pn
 //          that cannot be deferred, not instantiated at present)
 // y goes to every rank's activation buffer (dst); while it is at hand the CTA's share of the next layer's v_j . y (j < m) is formed.
 template <int UPD>
-__device__ __forceinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
+__device__ __noinline__ void panel_rows(double *W, int ld, Panel pn, const double *xs, const double *dsl, double lr,
                                            int act_kind, const Dst &dst, int segs, double *zpart, const double *us,
                                            const double *coef, int mcorr, int m, const DotOut &dots, double *red,
                                            double *ykeep = nullptr, bool z_ready = false) {
@@ -880,8 +885,13 @@ __device__ __forceinline__ void train_sample_lazy1_body(const KP &p, const int g
         if (pn.cnt > 0) {
           // a layer share that fits L2 is read again soon (top-down of layer 1 -> its forward pass, forward
           // of the top layer -> its top-down pass): keep it cached; otherwise stream with evict-first
-          if (p.keep_l2) panel_cols_read<false>(n.W[l], n.ld[l], pn, dsl, Pout);
-          else panel_cols_read<true>(n.W[l], n.ld[l], pn, dsl, Pout);
+          if (p.items_in_flight >= 3) {
+            if (p.keep_l2) panel_cols_read<false, 3>(n.W[l], n.ld[l], pn, dsl, Pout);
+            else panel_cols_read<true, 3>(n.W[l], n.ld[l], pn, dsl, Pout);
+          } else {
+            if (p.keep_l2) panel_cols_read<false, 2>(n.W[l], n.ld[l], pn, dsl, Pout);
+            else panel_cols_read<true, 2>(n.W[l], n.ld[l], pn, dsl, Pout);
+          }
         }
       } else if (pn.cnt > 0) {
         if (bpm) panel_cols_bpm<TG>(n.W[l], n.dW[l], n.ld[l], pn, dsl, h, p.lr, p.alpha, Pout);
@@ -1148,6 +1158,11 @@ int prepare_lazy1(const KP &p_in, int grid, KP &p_out, size_t &smem_out) {
       const char *e = getenv("HPNN_FOLD_OUT");
       return (e && !strcmp(e, "0")) ? 0 : 1;
     }();
+    static const int depth_env = [] {
+      const char *e = getenv("HPNN_ITEMS_IN_FLIGHT");
+      return e ? atoi(e) : 3;  // 7-row panels: 162.7 vs 166.9 us per iteration with 2; wide panels: no difference
+    }();
+    p.items_in_flight = depth_env;
     static const int keep_env = [] {
       const char *e = getenv("HPNN_L2_KEEP");
       return e ? atoi(e) : -1;
