@@ -21,6 +21,7 @@ def help_text(prog: str, train: bool) -> str:
     s += "--backend cuda|cpu|torch \tengine (extension).\n--lr x \tlearning rate override (extension).\n"
     if not train:
         s += "--batch n \tsamples per launch, batched GEMM path (extension).\n"
+        s += "--precision fp64|bf16 \tbatched path: FP64 (default) or tensor-core bf16 (extension).\n"
     s += bar + "input:     neural network .def file\ncontains the network definition and\n"
     s += "topology. May contain weight values\nor context for a random generation.\n" + bar
     return s
@@ -28,7 +29,7 @@ def help_text(prog: str, train: bool) -> str:
 
 def parse(argv: List[str], prog: str, train: bool):
     opts = {"omp": None, "blas": None, "streams": 1, "dry": False, "backend": None, "lr": None, "batch": -1,
-            "conf": None, "help": False}
+            "precision": "fp64", "conf": None, "help": False}
     i = 1
 
     def bad(flag):
@@ -40,9 +41,9 @@ def parse(argv: List[str], prog: str, train: bool):
         a = argv[i]
         if a.startswith("--"):
             key = a[2:]
-            if key in ("backend", "lr", "batch") and i + 1 < len(argv):
+            if key in ("backend", "lr", "batch", "precision") and i + 1 < len(argv) and (train is False or key != "precision"):
                 val = argv[i + 1]
-                opts[key] = val if key == "backend" else (float(val) if key == "lr" else int(val))
+                opts[key] = val if key in ("backend", "precision") else (float(val) if key == "lr" else int(val))
                 i += 2
                 continue
             sys.stderr.write("syntax error: unrecognized option!\n")

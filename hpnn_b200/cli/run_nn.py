@@ -25,7 +25,11 @@ def main(argv=None) -> int:
         log.nn_error(str(e) + "\n")
         sys.stderr.write("FAILED to read NN configuration file! (ABORTING)\n")
         return 255
-    run_kernel(conf, backend=o["backend"], batch=o["batch"])
+    try:
+        run_kernel(conf, backend=o["backend"], batch=o["batch"], precision=o["precision"])
+    except ValueError as e:  # an extension option that does not fit the chosen back-end
+        log.nn_error(str(e) + "\n")
+        return 255
     return 0
 
 

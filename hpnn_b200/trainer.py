@@ -371,14 +371,19 @@ def classify_batch(Y: np.ndarray, T: np.ndarray, nn_type: int):
     return guess, want, res
 
 
-def run_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, batch: int = -1, **engine_kw) -> dict:
+def run_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, batch: int = -1, precision: str = "fp64",
+               **engine_kw) -> dict:
     """``nn_run_kernel`` (src/libhpnn.c:1306-1536).  Returns ``{"pass": n, "total": n}``.
 
     The reference evaluates one file per launch (and so does ``batch=0``).  By default
     (``batch=-1``) the CUDA back-end parses the whole directory with the native parallel reader and
     pushes it through the batched FP64 forward ``HPNN_RUN_BATCH`` (1024) samples at a time; verdicts
     and output lines are identical, only produced ~20x faster.  Verbosity 3 (per-class tables) and
-    the other back-ends keep the per-file loop."""
+    the other back-ends keep the per-file loop.  ``precision="bf16"`` (extension, batched CUDA path only)
+    evaluates the layers on the tcgen05 tensor cores (bf16 operands, fp32 accumulation, FP64 outputs): the
+    probabilities agree with FP64 to about 1e-3, a verdict can differ where two classes are that close."""
+    if precision not in ("fp64", "bf16"):
+        raise ValueError(f"unknown precision {precision!r}")
     out = stream or sys.stdout
     stats = {"pass": 0, "total": 0}
     if conf.kernel is None or conf.tests is None or conf.type not in (N.TYPE_ANN, N.TYPE_SNN):
@@ -392,6 +397,8 @@ def run_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, batch: 
     backend = backend or default_backend()
     if batch < 0:
         batch = int(os.environ.get("HPNN_RUN_BATCH", "1024")) if (backend == "cuda" and len(files) > 1) else 0
+    if precision != "fp64" and not (batch > 0 and backend == "cuda"):
+        raise ValueError("precision='bf16' needs the batched CUDA path (backend cuda, batch > 0)")
     eng = make_engine(backend, conf.kernel, conf.type, N.TRAIN_BP, **engine_kw)
     try:
         outputs = {}
@@ -400,7 +407,7 @@ def run_kernel(conf: NNConf, backend: Optional[str] = None, stream=None, batch: 
             Ys = []
             for b0 in range(0, len(sset), batch):
                 X = sset.inputs[b0:b0 + batch].to(eng.net.device, non_blocking=True)
-                Ys.append(eng.net.forward_batch(X, engine_kw.get("stable_softmax", False)))
+                Ys.append(eng.net.forward_batch(X, engine_kw.get("stable_softmax", False), precision=precision))
             if Ys and log.get_verbose() < 3 and len(sset) == len(files):
                 # whole-directory fast path: vectorised verdicts, one write for all lines
                 Y = torch.cat(Ys).cpu().numpy()

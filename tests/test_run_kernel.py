@@ -61,3 +61,47 @@ def test_batched_default_prints_the_per_file_lines(tmp_path, nn_type, name):
         assert np.allclose(pa, pb, atol=1e-8)
     else:
         assert la == lb
+
+
+@pytest.mark.gpu
+def test_bf16_precision_option_agrees_with_fp64(tmp_path):
+    """run_kernel(precision="bf16"): the tensor-core chain gives the FP64 path's probabilities to ~1e-3 and the
+    same verdicts wherever the best two classes are further apart than that; refused off the batched CUDA path."""
+    from conftest import write_conf
+
+    nn_type, n_in, n_out = N.TYPE_SNN, 70, 5
+    X, T = make_problem(nn_type, n_in, (48, 40), n_out, n_samples=200, seed=5)
+    (tmp_path / "samples").mkdir()
+    (tmp_path / "tests").mkdir()
+    for i, (x, t) in enumerate(zip(X, T)):
+        hp.write_sample(str(tmp_path / "tests" / f"s{i:03d}.txt"), x, t, str(i % n_out))
+    write_conf(tmp_path / "nn.conf", nn_type="SNN", n_in=n_in, hid="48 40", n_out=n_out, samples=str(tmp_path / "samples"),
+               tests=str(tmp_path / "tests"))
+    conf = hp.load_conf(str(tmp_path / "nn.conf"))
+    log.set_verbose(2)
+    try:
+        a, b = io.StringIO(), io.StringIO()
+        sa = hp.run_kernel(conf, backend="cuda", stream=a)
+        sb = hp.run_kernel(conf, backend="cuda", stream=b, precision="bf16")
+    finally:
+        log.set_verbose(0)
+    assert sa["total"] == sb["total"] == 200
+    la, lb = a.getvalue().splitlines(), b.getvalue().splitlines()
+    pa = np.array([float(l.split(" P=")[1].split()[0]) for l in la])
+    pb = np.array([float(l.split(" P=")[1].split()[0]) for l in lb])
+    assert np.allclose(pa, pb, atol=0.5)  # percent: 5e-3 in probability
+    same = sum(x.split(" P=")[0] == y.split(" P=")[0] for x, y in zip(la, lb))
+    assert same >= 190 and abs(sa["pass"] - sb["pass"]) <= 10
+    with pytest.raises(ValueError):
+        hp.run_kernel(conf, backend="cuda", batch=0, precision="bf16")
+    with pytest.raises(ValueError):
+        hp.run_kernel(conf, backend="cpu", precision="bf16")
+
+
+def test_cli_accepts_precision_only_for_run_nn():
+    from hpnn_b200.cli._common import parse
+
+    o = parse(["run_nn", "--precision", "bf16", "--batch", "64", "nn.conf"], "run_nn", False)
+    assert o["precision"] == "bf16" and o["batch"] == 64 and o["conf"] == "nn.conf"
+    with pytest.raises(SystemExit):
+        parse(["train_nn", "--precision", "bf16", "nn.conf"], "train_nn", True)
