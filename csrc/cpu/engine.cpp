@@ -7,6 +7,7 @@
 //   sample loops src/ann.c:2281-2467, src/snn.c:1417-1595
 // written as one generic L-layer loop instead of the reference's per-BLAS-flavour copies.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #ifdef _OPENMP
 #include <omp.h>
@@ -243,7 +244,19 @@ void update_forward(hpnn_kernel *k, int type, int stable, bool momentum, double 
 namespace packed {
 
 constexpr int RB = 8;
-typedef double v4 __attribute__((vector_size(32), aligned(8)));
+// Naturally aligned vector types (attributes such as aligned(8) are dropped from template arguments, so the
+// packed weights -- 16-byte aligned at best -- are always reached through loadu / storeu).
+typedef double v4 __attribute__((vector_size(32)));
+template <typename V>
+__attribute__((always_inline)) inline V loadu(const double *p) {
+  V v;
+  __builtin_memcpy(&v, p, sizeof(V));
+  return v;
+}
+template <typename V>
+__attribute__((always_inline)) inline void storeu(double *p, V v) {
+  __builtin_memcpy(p, &v, sizeof(V));
+}
 
 inline int nblk(int N) { return (N + RB - 1) / RB; }
 
@@ -265,75 +278,101 @@ void unpack(const std::vector<double> &P, int N, int M, double *W) {
 
 // NB blocks (8*NB rows) of one layer: optional update (UPD: 0 none, 1 BP, 2 BPM), then the dot
 // products with x; sums[8*NB].  sc[8*NB] = lr * delta of the rows (0 for padding rows).
-template <int NB, int UPD>
+// V is a vector of VW doubles (4: AVX2 / generic, 8: AVX-512, one vector = one block of 8 rows).
+template <typename V, int VW, int NB, int UPD>
 __attribute__((always_inline)) inline void rows_pass(double *P, double *Mo, int M, const double *sc, const double *h,
                                                      const double *x, double alpha, double *sums) {
-  constexpr int NV = 2 * NB;
-  v4 acc[NV], s[NV];
+  constexpr int VPB = RB / VW;  // vectors per block
+  constexpr int NV = VPB * NB;
+  V acc[NV], s[NV];
   for (int j = 0; j < NV; ++j) {
-    acc[j] = v4{0.0, 0.0, 0.0, 0.0};
-    s[j] = v4{sc[4 * j], sc[4 * j + 1], sc[4 * j + 2], sc[4 * j + 3]};
+    V z = {}, t = {};
+    for (int q = 0; q < VW; ++q) t[q] = sc[VW * j + q];
+    acc[j] = z;
+    s[j] = t;
   }
-  const v4 av = v4{alpha, alpha, alpha, alpha};
   const size_t bstride = (size_t)M * RB;
   for (int c = 0; c < M; ++c) {
     const double hc = UPD ? h[c] : 0.0, xc = x[c];
-    const v4 hb = v4{hc, hc, hc, hc}, xb = v4{xc, xc, xc, xc};
     for (int j = 0; j < NV; ++j) {
-      double *p = P + (size_t)(j >> 1) * bstride + (size_t)c * RB + (j & 1) * 4;
-      v4 w = *reinterpret_cast<v4 *>(p);
+      double *p = P + (size_t)(j / VPB) * bstride + (size_t)c * RB + (j % VPB) * VW;
+      V w = loadu<V>(p);
       if (UPD == 1) {
-        const v4 t = s[j] * hb;
+        const V t = s[j] * hc;  // (scalar operands are broadcast)
         w = w + t;
-        *reinterpret_cast<v4 *>(p) = w;
+        storeu<V>(p, w);
       } else if (UPD == 2) {
         double *pm = Mo + (p - P);
-        v4 m = *reinterpret_cast<v4 *>(pm);
-        const v4 t = s[j] * hb;
+        V m = loadu<V>(pm);
+        const V t = s[j] * hc;
         m = m + t;
         w = w + m;
-        *reinterpret_cast<v4 *>(p) = w;
-        m = m * av;
-        *reinterpret_cast<v4 *>(pm) = m;
+        storeu<V>(p, w);
+        m = m * alpha;
+        storeu<V>(pm, m);
       }
-      const v4 t2 = w * xb;
+      const V t2 = w * xc;
       acc[j] = acc[j] + t2;
     }
   }
   for (int j = 0; j < NV; ++j)
-    for (int q = 0; q < 4; ++q) sums[4 * j + q] = acc[j][q];
+    for (int q = 0; q < VW; ++q) sums[VW * j + q] = acc[j][q];
 }
 
-// blocks [b0, b1) of one layer, in groups of 4 / 2 / 1
-template <int UPD>
+// blocks [b0, b1) of one layer, in groups of GMAX / ... / 2 / 1 blocks: enough independent row sums in
+// flight to hide the add latency (8 vectors: 4 blocks of two v4, 8 blocks of one v8)
+template <typename V, int VW, int GMAX, int UPD>
 __attribute__((always_inline)) inline void blocks_pass(double *P, double *Mo, int M, int b0, int b1, const double *sc,
                                                        const double *h, const double *x, double alpha, double *sums) {
   const size_t bstride = (size_t)M * RB;
   int b = b0;
-  for (; b + 4 <= b1; b += 4) rows_pass<4, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
-  for (; b + 2 <= b1; b += 2) rows_pass<2, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
-  for (; b < b1; ++b) rows_pass<1, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
+  if (GMAX >= 8)
+    for (; b + 8 <= b1; b += 8)
+      rows_pass<V, VW, 8, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
+  for (; b + 4 <= b1; b += 4)
+    rows_pass<V, VW, 4, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
+  for (; b + 2 <= b1; b += 2)
+    rows_pass<V, VW, 2, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
+  for (; b < b1; ++b)
+    rows_pass<V, VW, 1, UPD>(P + b * bstride, Mo ? Mo + b * bstride : nullptr, M, sc + b * RB, h, x, alpha, sums + b * RB);
+}
+
+template <typename V, int VW, int GMAX>
+__attribute__((always_inline)) inline void blocks_any(int upd, double *P, double *Mo, int M, int b0, int b1, const double *sc,
+                                                      const double *h, const double *x, double alpha, double *sums) {
+  if (upd == 0) blocks_pass<V, VW, GMAX, 0>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
+  else if (upd == 1) blocks_pass<V, VW, GMAX, 1>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
+  else blocks_pass<V, VW, GMAX, 2>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
 }
 
 void blocks_default(int upd, double *P, double *Mo, int M, int b0, int b1, const double *sc, const double *h,
                     const double *x, double alpha, double *sums) {
-  if (upd == 0) blocks_pass<0>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
-  else if (upd == 1) blocks_pass<1>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
-  else blocks_pass<2>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
+  blocks_any<v4, 4, 4>(upd, P, Mo, M, b0, b1, sc, h, x, alpha, sums);
 }
 #if defined(__x86_64__)
 __attribute__((target("avx2"))) void blocks_avx2(int upd, double *P, double *Mo, int M, int b0, int b1, const double *sc,
                                                  const double *h, const double *x, double alpha, double *sums) {
-  if (upd == 0) blocks_pass<0>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
-  else if (upd == 1) blocks_pass<1>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
-  else blocks_pass<2>(P, Mo, M, b0, b1, sc, h, x, alpha, sums);
+  blocks_any<v4, 4, 4>(upd, P, Mo, M, b0, b1, sc, h, x, alpha, sums);
+}
+// AVX-512: one 64-byte vector per block of 8 rows.  AVX-512F contains fused multiply-add, so this file is
+// compiled with -ffp-contract=off: every product and every sum is rounded on its own, as in the reference.
+typedef double v8 __attribute__((vector_size(64)));
+__attribute__((target("avx512f"))) void blocks_avx512(int upd, double *P, double *Mo, int M, int b0, int b1, const double *sc,
+                                                      const double *h, const double *x, double alpha, double *sums) {
+  blocks_any<v8, 8, 8>(upd, P, Mo, M, b0, b1, sc, h, x, alpha, sums);
 }
 #endif
 typedef void (*blocks_fn)(int, double *, double *, int, int, int, const double *, const double *, const double *, double,
                           double *);
 blocks_fn pick_blocks() {
 #if defined(__x86_64__)
-  if (__builtin_cpu_supports("avx2")) return blocks_avx2;
+  // HPNN_CPU_ISA = avx512 | avx2 | generic.  Default avx2: on the 784-300-10 tutorial net the 64-byte path is no
+  // faster (34.4 k vs 35.3 k iterations/s with 4 threads: the pass is bound by L2 traffic, not by the adds).
+  const char *isa = getenv("HPNN_CPU_ISA");
+  const bool want512 = isa && !strcmp(isa, "avx512");
+  const bool want2 = !isa || want512 || !strcmp(isa, "avx2");
+  if (want512 && __builtin_cpu_supports("avx512f")) return blocks_avx512;
+  if (want2 && __builtin_cpu_supports("avx2")) return blocks_avx2;
 #endif
   return blocks_default;
 }

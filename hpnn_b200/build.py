@@ -23,7 +23,7 @@ BINDIR = ROOT / "build" / "bin"
 
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp,-Wall,-Wno-unused-function",
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp,-Wall,-Wno-unused-function,-ffp-contract=off",
           f"-I{ROOT / 'include'}", f"-I{ROOT / 'csrc' / 'core'}", f"-I{ROOT / 'csrc' / 'kernels'}"]
 COMMON += os.environ.get("HPNN_EXTRA_NVCC_FLAGS", "").split()  # experiments, e.g. -DHPNN_W_STREAM
 

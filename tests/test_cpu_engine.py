@@ -148,3 +148,23 @@ def test_deep_network_beyond_the_device_cap(tmp_path):
     assert r.n_iter >= 1 and np.isfinite(r.last_err)
     assert cpu.run(np.linspace(0.1, 0.9, 7)).shape == (3,)
     cpu.close()
+
+
+@pytest.mark.parametrize("train", [N.TRAIN_BP, N.TRAIN_BPM])
+def test_simd_paths_are_bit_identical(train, monkeypatch):
+    """HPNN_CPU_ISA = generic | avx2 | avx512 (the wider ones only where the CPU has them): every path performs the
+    reference's operations in the reference's order, products and sums rounded separately (no FMA contraction),
+    so the trained weights agree to the last bit.  150 rows exercise the 8-, 4-, 2- and 1-block groups."""
+    results = []
+    for isa in ("generic", "avx2", "avx512"):
+        monkeypatch.setenv("HPNN_CPU_ISA", isa)
+        k, _ = hp.generate_kernel(5, 33, [150, 21], 7)
+        X, T = make_problem(N.TYPE_ANN, 33, (150, 21), 7, n_samples=2, seed=4)
+        eng = CpuEngine(k, N.TYPE_ANN, train, max_iter=40, min_iter=40)
+        iters = [eng.train(x, t).n_iter for x, t in zip(X, T)]
+        results.append((iters, [w.copy() for w in eng.kernel().weights]))
+        eng.close()
+    for iters, ws in results[1:]:
+        assert iters == results[0][0]
+        for a, b in zip(ws, results[0][1]):
+            assert np.array_equal(a, b)
