@@ -26,7 +26,8 @@ struct KP {
   long long *trace;  // optional phase trace: (tag, clock64) pairs written by CTA 0, thread 0
   int trace_cap;
   int items_in_flight;  // row items (4 x 16 bytes per thread) the read-only top-down pass keeps in flight: 2 or 3
-  int trace_ns;  // phase stamps in nanoseconds (%globaltimer) instead of SM cycles: HPNN_TRACE_NS=1
+  int trace_ns;
+  int jitter_ns;  // > 0: schedule perturbation (tests): random delays of up to this many ns before every arrival / hand-over  // phase stamps in nanoseconds (%globaltimer) instead of SM cycles: HPNN_TRACE_NS=1
   int keep_l2;   // K-PL1: a rank's share of a layer fits L2, so the passes use caching loads instead of evict-first ones
   int slicewise;  // K-PL1, several ranks, short panels: forward passes consume the peers' activations slice by slice
   int fold_out;  // K-PL1: the output layer is folded into the phases of the layer below (see train_lazy1.cu)
@@ -55,6 +56,7 @@ struct WatchState {
   unsigned long long budget_ns;
   unsigned tripped;   // a thread of this CTA gave up or saw the abort word
   unsigned exit_now;  // CTA-uniform copy, written by thread 0 once per iteration
+  unsigned jitter_ns; // schedule perturbation, see jitter()
 };
 static __shared__ WatchState s_watch;
 static __shared__ unsigned s_kx;  // cross-rank barrier index of the last arrive (for Barrier::wait_rank)
@@ -75,8 +77,23 @@ __device__ __forceinline__ void watch_init(const KP &p) {
     s_watch.budget_ns = p.spin_budget_ns;
     s_watch.tripped = 0;
     s_watch.exit_now = 0;
+    s_watch.jitter_ns = p.jitter_ns > 0 ? (unsigned)p.jitter_ns : 0u;
   }
   __syncthreads();
+}
+// Schedule perturbation (hpnn_dev_set_jitter_ns; the stand-in for a race detector on a pool where
+// compute-sanitizer is closed): a pseudo-random delay before every barrier arrival, cross-rank signal and
+// tagged store.  All summation orders are fixed, so a run with delays must reproduce the undisturbed run bit
+// for bit; a hand-over that only works because "the other side is always later" shows up as a difference.
+__device__ __forceinline__ void jitter(unsigned salt) {
+  const unsigned j = s_watch.jitter_ns;
+  if (j != 0u) {
+    unsigned h = ((unsigned)blockIdx.x * 2654435761u) ^ (salt * 40503u) ^ ((unsigned)threadIdx.x * 97u) ^ (unsigned)clock64();
+    h ^= h >> 13;
+    h *= 0x5bd1e995u;
+    h ^= h >> 15;
+    __nanosleep(h % j);
+  }
 }
 // slow path of a spin: true = stop waiting
 static __device__ __noinline__ bool spin_check(unsigned long long &t0) {
@@ -152,6 +169,7 @@ struct Barrier {
       unsigned *c = sync + 32 * (k % 3u);
       unsigned *prev = sync + 32 * ((k + 2u) % 3u);
       ++k;
+      jitter(k);
       red_add_release_gpu(c, 1u);
       Spin sp;
       while (ld_relaxed_gpu(c) != grid) {
@@ -190,6 +208,7 @@ struct Barrier {
       ++k;
       ++kx;
       s_kx = kx;
+      jitter(k);
       red_add_release_gpu(c, 1u);
       if (bid == 0) {
         Spin sp;
@@ -198,6 +217,7 @@ struct Barrier {
         }
         *prev = 0;
         fence_sys();
+        jitter(k + 7u);
         signal(n, true);
       }
     }
@@ -234,6 +254,7 @@ struct Barrier {
       // cumulative, so that fence orders every local CTA's peer stores before the flag.  A fence.sys
       // costs ~2.5 us on this part (measured: barrier with three of them 10.8 us, grid barrier 2 us).
       (void)remote;
+      jitter(k);
       red_add_release_gpu(c, 1u);
       Spin sp;
       if (n.world == 1) {
@@ -257,6 +278,7 @@ struct Barrier {
           }
           *prev = 0;
           fence_sys();  // release: everything this rank wrote is visible before the counter moves
+          jitter(k + 7u);
           signal(n);
         }
         const unsigned long long *ctr = reinterpret_cast<const unsigned long long *>(n.arena[n.rank] + n.off_flags) + kCounterSlot;
@@ -280,6 +302,7 @@ struct Barrier {
 // SYS selects system scope (peer memory) instead of GPU scope.
 template <bool SYS>
 __device__ __forceinline__ void st_pair(double *base, long long idx, double v, unsigned long long tag) {
+  jitter((unsigned)idx);
   if (SYS) st_b128_relaxed_sys(base + 2 * idx, (unsigned long long)__double_as_longlong(v), tag);
   else st_b128_relaxed_gpu(base + 2 * idx, (unsigned long long)__double_as_longlong(v), tag);
 }

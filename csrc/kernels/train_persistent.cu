@@ -246,6 +246,7 @@ extern long long g_lazy_min_bytes;
 static int g_grid_override = 0;
 static long long g_spin_timeout_ms = -1;  // -1: HPNN_SPIN_TIMEOUT_MS or 10 s
 static int g_fault_kind = 0, g_fault_rank = -1;
+static int g_jitter_ns = 0;
 static long long *g_trace = nullptr;
 static int g_trace_cap = 0;
 static thread_local char g_err[512] = "";
@@ -283,6 +284,8 @@ long long hpnn_abi_sizeof(int which) {
 void hpnn_dev_set_persistent_grid(int ctas) { g_grid_override = ctas; }
 
 void hpnn_dev_set_spin_timeout_ms(long long ms) { g_spin_timeout_ms = ms; }
+
+void hpnn_dev_set_jitter_ns(int ns) { g_jitter_ns = ns > 0 ? ns : 0; }
 
 void hpnn_dev_set_fault(int kind, int rank) {
   g_fault_kind = kind;
@@ -431,6 +434,7 @@ static int build_kp(const hpnn_dev_net *net, const hpnn_train_opts *o, int mode,
     const long long ms = g_spin_timeout_ms >= 0 ? g_spin_timeout_ms : env_ms;
     p.spin_budget_ns = ms > 0 ? (unsigned long long)ms * 1000000ull : 0ull;
     p.fault = (g_fault_kind == 1 && g_fault_rank == net->rank) ? 1 : 0;
+    p.jitter_ns = g_jitter_ns;
   }
   p.trace = g_trace;
   p.trace_cap = g_trace_cap;

@@ -112,6 +112,7 @@ def _declare(lib):
         "hpnn_dev_train_sample_vranks": (i, [C.POINTER(DevNet), i, C.POINTER(TrainOpts), i, C.POINTER(vp), vp]),
         "hpnn_dev_set_spin_timeout_ms": (None, [ll]),
         "hpnn_dev_set_fault": (None, [i, i]),
+        "hpnn_dev_set_jitter_ns": (None, [i]),
         "hpnn_dev_persistent_grid": (i, []),
         "hpnn_dev_set_persistent_grid": (None, [i]),
         "hpnn_dev_set_lazy": (None, [i, C.c_longlong]),

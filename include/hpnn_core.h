@@ -271,6 +271,10 @@ void hpnn_dev_set_spin_timeout_ms(long long ms);
 /* Fault injection for tests: kind 1 = the kernels launched for rank `rank` return at once, as if that
  * rank's launch had failed; kind 0 = off. */
 void hpnn_dev_set_fault(int kind, int rank);
+/* Schedule perturbation for tests: ns > 0 makes every barrier arrival, cross-rank signal and tagged store of the
+ * trainers wait a pseudo-random time of up to ns nanoseconds first.  All summation orders are fixed, so the
+ * results must not change by a single bit (tests/test_gpu_vranks.py); 0 = off. */
+void hpnn_dev_set_jitter_ns(int ns);
 /* number of co-resident CTAs the persistent kernel will use on this device */
 int hpnn_dev_persistent_grid(void);
 /* set grid (CTAs) used by K-P: 0 = one per SM (default) */

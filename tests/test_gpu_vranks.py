@@ -127,3 +127,41 @@ def test_missing_rank_is_reported_not_waited_for(monkeypatch, proto):
     assert a.n_iter == b.n_iter and abs(a.last_err - b.last_err) < 1e-12
     eng.close()
     cpu.close()
+
+
+@pytest.mark.parametrize("backend,proto,panel", [("virtual:4", "barrier", False), ("virtual:4", "tagged", False),
+                                                 ("virtual:4", "barrier", True), ("virtual:3", "tagged", True),
+                                                 ("cuda", "barrier", False)])
+def test_schedule_perturbation_changes_no_bit(monkeypatch, backend, proto, panel):
+    """The stand-in for a race detector (compute-sanitizer is closed on the pool): with pseudo-random delays of up to
+    3 us before every barrier arrival, cross-rank signal and tagged store (hpnn_dev_set_jitter_ns) the trainers
+    must reproduce the undisturbed run bit for bit -- all summation orders are fixed, so any difference would be
+    a hand-over that only works because the other side happens to be later.  Virtual ranks: K-P with both
+    protocols, the row-panel trainer K-PL1 with both; "cuda": the shared-memory-resident K-PR (tagged pairs only)."""
+    monkeypatch.setenv("HPNN_TP_PROTOCOL", proto)
+    lib = N.load()
+    if panel:
+        lib.hpnn_dev_set_lazy(8, 0)
+        lib.hpnn_dev_set_lazy_panel(1)
+    try:
+        dims = (40, (600, 300, 150), 12) if panel else (40, (37, 29), 6)
+        n_it = 21 if panel else 45
+        kw = dict(max_iter=n_it - 1, min_iter=n_it + 10, delta=1e-300)
+        runs = []
+        for jitter in (0, 3000, 700):
+            lib.hpnn_dev_set_jitter_ns(jitter)
+            k, _ = hp.generate_kernel(9, dims[0], list(dims[1]), dims[2])
+            X, T = make_problem(N.TYPE_SNN, dims[0], dims[1], dims[2], n_samples=2, seed=8)
+            eng = make_engine(backend, k, N.TYPE_SNN, N.TRAIN_BPM if not panel else N.TRAIN_BP, **kw)
+            res = [eng.train(x, t) for x, t in zip(X, T)]
+            runs.append(([r.n_iter for r in res], [r.last_err for r in res], [w.copy() for w in eng.kernel().weights]))
+            eng.close()
+        for iters, errs, ws in runs[1:]:
+            assert iters == runs[0][0] == [n_it, n_it]
+            assert errs == runs[0][1]
+            for a, b in zip(ws, runs[0][2]):
+                assert np.array_equal(a, b)
+    finally:
+        lib.hpnn_dev_set_jitter_ns(0)
+        lib.hpnn_dev_set_lazy(-1, -1)
+        lib.hpnn_dev_set_lazy_panel(-1)
