@@ -46,9 +46,9 @@ namespace umma {
 constexpr int BM = 128, BN = 256, BK = 64;       // tile (BK bf16 = one 128-byte swizzle row); N = 256 halves the
                                                  // shared-memory bytes per flop (A is read once per 256 columns)
 constexpr int UMMA_K = 16;                       // bf16 MMA depth
-constexpr int STAGES = 3;                        // 3 x 48 KB ring, one persistent CTA per SM
+constexpr int STAGES = 3;                        // 3 x 48 KB ring (one-CTA and multicast kernels; the pair kernel: 5 x 32 KB)
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;   // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;   // 16 + 32 = 48 KB
 constexpr int TMEM_COLS = 2 * BN;                // two fp32 accumulators of BN columns: the whole TMEM
 constexpr int THREADS = 192;
 constexpr int OUT_BYTES = BM * BN * 2;           // bf16 output tile staged for the TMA store (64 KB)
@@ -152,7 +152,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// instruction descriptor: D=f32, A=B=bf16, both K-major, N=128, M=128
+// instruction descriptor: D=f32, A=B=bf16, both K-major, N=256, M=128
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
