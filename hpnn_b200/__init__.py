@@ -12,7 +12,7 @@ from .kernel_io import Kernel, dump_kernel, generate_kernel, load_kernel
 from .samples import read_sample, shuffle_order, walk, write_sample
 from .trainer import make_engine, run_kernel, train_kernel
 
-__version__ = "0.1.0"
+__version__ = "0.2.0"
 
 __all__ = ["NNConf", "load_conf", "parse_conf", "dump_conf", "Kernel", "generate_kernel", "load_kernel",
            "dump_kernel", "read_sample", "write_sample", "walk", "shuffle_order", "train_kernel", "run_kernel",
